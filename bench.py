@@ -1,0 +1,386 @@
+#!/usr/bin/env python3
+"""bench.py — the HBM probe of BASELINE.json (`metric`: HBM probe GB/s per GPU; full-box
+health-sweep seconds), measured through the C ABI of libgpuprobe.so.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo (CUDA, sm_100a)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU port of the spec on host cores
+
+One "step" = one pass of the hot path over one batch of synthetic device-resident
+input (gp_hbm_step, include/gpuprobe.h): fill X (walking-ones) -> copy X->Y -> verify Y ->
+fill X (address-in-address) -> verify X -> triad Z=b+3c -> checksum Z, over 16 GiB per
+array (BASELINE.json configs[1]).  Algorithmic bytes per step = 10 * bytes
+(fill N, copy 2N, verify N, triad 3N).  Every step's three 48-byte results
+are read back to the host and checked against closed forms inside the timed region.
+
+Multi-GPU (torchrun, one rank per GPU): the path shards as independent devices, so
+ranks run the same per-GPU workload with no data-path collective ("scaling": "weak");
+torch.distributed (NCCL) is used only for the barrier and the max-over-ranks time.
+
+The reference (uppercaveman/k8s-gpu-device-plugin) has no implementation of this path
+(benchmark/benchmark.go is a pprof wrapper) and no Go toolchain exists here, so the
+`--impl reference` arm and `cpu_baseline` time this repo's CPU port of the frozen spec
+(oracle/gpuprobe_oracle.c, kind "port") — the one place bench.py executes oracle/.
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "k8s-gpu-device-plugin_b200"))
+
+M64 = (1 << 64) - 1
+GIB = 1 << 30
+UNIT = "GB/s"
+METRIC = "hbm_probe_gbps"
+
+
+def closed_forms(nwords, step):
+    """Expected (sum, xor) of the step's two pattern verifies — SURVEY.md §8(c) closed forms."""
+    wo = ((-(nwords // 64)) & M64, 0 if (nwords // 64) % 2 == 0 else M64)
+    big_x = lambda m: [m, 1, m + 1, 0][m % 4]
+    s, x = (4 * nwords * (nwords - 1)) & M64, (8 * big_x(nwords - 1)) & M64
+    if step & 1:
+        s, x = (nwords * M64 - s) & M64, x ^ (M64 if nwords % 2 else 0)
+    return wo, (s, x)
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            v = float(json.load(f)["hbm_gbs"])
+        return v, "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML)."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
+               0x2: "applications_clocks_setting", 0x10: "sync_boost"}
+
+    def __init__(self, index, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.stop_ev = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as e:  # no NVML: report that, do not invent clocks
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        while not self.stop_ev.is_set():
+            try:
+                self.samples.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                try:
+                    mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self.stop_ev.wait(self.period)
+
+    def finish(self):
+        self.stop_ev.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "NVML unavailable"}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def dist_env():
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
+            int(os.environ.get("WORLD_SIZE", "1")))
+
+
+# ------------------------------------------------------------------ CPU port ----------------
+def cpu_port_run(nbytes, steps, warmup, min_seconds=0.0, max_seconds=30.0):
+    """Times the CPU port of the step (oracle/) with every host thread.  Returns a dict."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import oracle_lib
+    lib = oracle_lib.load()
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    arena = np.zeros(5 * nbytes, dtype=np.uint8)  # first touch here
+    nwords = nbytes // 8
+    for w in range(max(warmup, 1)):
+        oracle_lib.hbm_step(lib, arena, nbytes, step=w, gen=(w == 0), nthreads=cores)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        out = oracle_lib.hbm_step(lib, arena, nbytes, step=done, gen=False, nthreads=cores)
+        wo, ad = closed_forms(nwords, done)
+        assert (out[0].sum, out[0].xor_, out[0].mismatches) == (wo[0], wo[1], 0)
+        assert (out[1].sum, out[1].xor_, out[1].mismatches) == (ad[0], ad[1], 0)
+        done += 1
+        el = time.perf_counter() - t0
+        if (done >= steps and el >= min_seconds) or el >= max_seconds:
+            break
+    el = time.perf_counter() - t0
+    return {"value": 10.0 * nbytes * done / el / 1e9, "seconds": el, "steps": done, "cores": cores,
+            "ms_per_step": el / done * 1e3,
+            "sample": f"{done} steps of the same 7-op step over {nbytes >> 20} MiB per array "
+                      f"(BASELINE.json configs[0] size) on {cores} threads"}
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    nbytes = args.cpu_bytes
+    r = cpu_port_run(nbytes, args.steps, max(args.warmup, 1), max_seconds=120.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": r["steps"], "warmup": max(args.warmup, 1), "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64+f32",
+        "data": "synthetic",
+        "config": {"workload": "1xB200 HBM stream probe: copy/triad + bit-exact pattern verify "
+                               "(BASELINE.json configs[1]); bounded CPU sample at configs[0] size",
+                   "bytes_per_array": nbytes, "arrays": 5, "algorithmic_bytes_per_step": 10 * nbytes,
+                   "host": "B200 host cores, no GPU"},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": r["sample"],
+                         "note": "CPU port of the frozen spec; the reference has no code for this path"},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------ CUDA arm ----------------
+def run_ours(args):
+    import gpuprobe
+    rank, local_rank, world = dist_env()
+    n_gpus = args.gpus
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the probe has no CPU fallback "
+                         "(use --impl reference for the CPU port)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    nbytes = args.bytes
+    nwords = nbytes // 8
+    variant = {"auto": 0, "vec": 1, "tma": 2}[args.variant]
+    probe = gpuprobe.Probe(keep_arena=1, hbm_bytes=nbytes, arena_cap_bytes=5 * nbytes + GIB,
+                           stream_variant=variant)
+    dev = probe.device_uuid(local_rank)
+
+    def check(out, step):
+        wo, ad = closed_forms(nwords, step)
+        if (out[0].sum, out[0].xor_, out[0].mismatches) != (wo[0], wo[1], 0):
+            raise SystemExit(f"step {step}: walking-ones verify of the copy destination failed: {out[0].astuple()}")
+        if (out[1].sum, out[1].xor_, out[1].mismatches) != (ad[0], ad[1], 0):
+            raise SystemExit(f"step {step}: address verify failed: {out[1].astuple()}")
+
+    triad_sig = None
+    for w in range(args.warmup):
+        out = probe.hbm_step(dev, nbytes, w)
+        check(out, w)
+        triad_sig = (out[2].sum, out[2].xor_, out[2].wsum)
+    probe.kernel_stats(dev, reset=True)
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        out = probe.hbm_step(dev, nbytes, k)   # blocks; 144 B of results come back D2H each step
+        check(out, k)
+        if triad_sig is not None and (out[2].sum, out[2].xor_, out[2].wsum) != triad_sig:
+            raise SystemExit(f"step {k}: triad checksum changed between steps")
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.finish()
+    stats = probe.kernel_stats(dev)
+    dev_ms = stats[gpuprobe.GP_K_STEP].total_ms
+
+    wall_max, dev_ms_max = wall, dev_ms
+    if dist is not None:
+        t = torch.tensor([wall, dev_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        wall_max, dev_ms_max = float(t[0]), float(t[1])
+
+    # ---- e2e: the call the plugin makes (gp_probe_device), cold arena, results to host -----
+    probe.close()
+    e2e_calls = max(1, min(args.steps, args.e2e_calls))
+    mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_TRIAD | gpuprobe.GP_PROBE_PATTERN
+    p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
+    p2.probe_device(dev, mask)  # warm-up call (context, module load)
+    p2.kernel_stats(dev, reset=True)
+    barrier()
+    t0 = time.perf_counter()
+    last = None
+    for _ in range(e2e_calls):
+        last = p2.probe_device(dev, mask)   # malloc arena, generate, warm up, time, verify, D2H, free
+        if not last.healthy:
+            raise SystemExit(f"e2e: gp_probe_device verdict unhealthy, failed_mask={last.failed_mask}")
+    barrier()
+    e2e_wall = time.perf_counter() - t0
+    st2 = p2.kernel_stats(dev)
+    e2e_bytes = sum(st2[i].algo_bytes for i in (gpuprobe.GP_K_COPY, gpuprobe.GP_K_TRIAD,
+                                                gpuprobe.GP_K_FILL, gpuprobe.GP_K_VERIFY))
+    e2e_launches = sum(int(st2[i].launches) for i in range(7))
+    if dist is not None:
+        t = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_wall = float(t[0])
+    d2h = ctypes.sizeof(gpuprobe.DeviceResult) + last.pattern_passes * 48 + 48 + 8
+
+    # ---- full-box sweep seconds (second half of the metric), rank 0, all N GPUs, one process --
+    sweep = None
+    if not args.no_sweep:
+        p2.trim()
+        barrier()
+        if rank == 0:
+            p3 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
+            try:
+                res, wall_cold = p3.probe_all(n_gpus, gpuprobe.GP_PROBE_ALL_SINGLE)
+                res, wall_warm = p3.probe_all(n_gpus, gpuprobe.GP_PROBE_ALL_SINGLE)
+                sweep = {"n_gpus": n_gpus, "seconds": wall_warm, "seconds_first_call": wall_cold,
+                         "healthy": [int(r.healthy) for r in res],
+                         "copy_gbps": [round(r.copy_gbps_median, 1) for r in res],
+                         "triad_gbps": [round(r.triad_gbps_median, 1) for r in res],
+                         "fill_gbps": [round(r.fill_gbps_median, 1) for r in res],
+                         "verify_gbps": [round(r.verify_gbps_median, 1) for r in res],
+                         "gemm_tflops": [round(r.gemm.tflops_median, 1) for r in res],
+                         "gemm_max_scaled_err": [r.gemm.max_scaled_err for r in res],
+                         "probes": "copy+triad+pattern(64+2 passes)+gemm, 16 GiB/array"}
+            except gpuprobe.GpuProbeError as e:
+                try:
+                    mask3 = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_TRIAD | gpuprobe.GP_PROBE_PATTERN
+                    res, wall_cold = p3.probe_all(n_gpus, mask3)
+                    res, wall_warm = p3.probe_all(n_gpus, mask3)
+                    sweep = {"n_gpus": n_gpus, "seconds": wall_warm, "seconds_first_call": wall_cold,
+                             "healthy": [int(r.healthy) for r in res], "probes": "copy+triad+pattern",
+                             "note": f"gemm probe unavailable: {e}"}
+                except gpuprobe.GpuProbeError as e2:
+                    sweep = {"error": str(e2)}
+            p3.close()
+        barrier()
+    p2.close()
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peak()
+    step_bytes = 10.0 * nbytes
+    value = step_bytes * args.steps * n_gpus / wall_max / 1e9
+    kernels = {}
+    for i in (gpuprobe.GP_K_COPY, gpuprobe.GP_K_TRIAD, gpuprobe.GP_K_FILL, gpuprobe.GP_K_VERIFY):
+        s = stats[i]
+        if s.launches:
+            ach = s.algo_bytes / (s.total_ms * 1e-3) / 1e9
+            kernels[gpuprobe.GP_K_NAMES[i]] = {
+                "launches": int(s.launches), "avg_ms": s.total_ms / s.launches,
+                "achieved_gbps": ach, "frac_of_measured_peak": ach / peak, "frac_of_8tbps": ach / 8000.0,
+                "share_of_step": s.total_ms / dev_ms if dev_ms else None}
+    dom = max(kernels, key=lambda k: kernels[k]["share_of_step"])
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(dom)
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbps"], "peak": peak,
+                "unit": "GB/s", "frac": kernels[dom]["achieved_gbps"] / peak, "traffic": traffic,
+                "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": {"copy": 2 * nbytes, "triad": 3 * nbytes,
+                                                 "fill": nbytes, "verify": nbytes}[dom]}
+    gpu_launches = sum(int(stats[i].launches) for i in range(7))
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": wall_max / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64+f32", "data": "synthetic",
+        "config": {"workload": "1xB200 HBM stream probe: 16 GiB copy/triad + bit-exact pattern verify "
+                               "(BASELINE.json configs[1]), per GPU",
+                   "bytes_per_array": nbytes, "arrays": 5, "algorithmic_bytes_per_step": int(step_bytes),
+                   "step": "fill WO, copy, verify, fill AiA, verify, triad, checksum",
+                   "stream_variant": args.variant, "parallelism": f"replicas x{n_gpus} (no collective)",
+                   "l2": "inputs (16 GiB per array) are larger than the 126 MB L2; no flush needed"},
+        "per_gpu_gbps": value / n_gpus, "frac_of_8tbps_per_gpu": value / n_gpus / 8000.0,
+        "device_ms_per_step": dev_ms_max / args.steps,
+        "roofline": roofline, "kernels": kernels, "clocks": clocks,
+        "e2e": {"value": e2e_bytes * n_gpus / e2e_wall / 1e9, "unit": UNIT,
+                "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h,
+                "calls": e2e_calls, "seconds_per_call": e2e_wall / e2e_calls,
+                "launches_per_call": e2e_launches // e2e_calls,
+                "what": "gp_probe_device(uuid, COPY|TRIAD|PATTERN) through the C ABI with a cold arena: "
+                        "cudaMalloc, operand generation, warm-up + timed launches, 64+2 fill/verify "
+                        "passes, verification, results copied to the caller's host struct, cudaFree. "
+                        "The probe takes no bulk host input by construction (patterns are generated "
+                        "on the device it grades), so h2d is 0 and d2h is the result bytes."},
+        "gpu_launches": gpu_launches,
+    }
+    if sweep is not None:
+        line["sweep"] = sweep
+    if n_gpus == 1 and not args.no_cpu:
+        c = cpu_port_run(args.cpu_bytes, 1, 1, min_seconds=10.0, max_seconds=30.0)
+        line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
+                                "sample": c["sample"],
+                                "note": "CPU port of the frozen spec (oracle/); the reference has no "
+                                        "code for this path"}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bytes", type=int, default=16 * GIB, help="bytes per array (default 16 GiB)")
+    ap.add_argument("--cpu-bytes", type=int, default=256 << 20, help="bytes per array of the CPU sample")
+    ap.add_argument("--variant", default="auto", choices=["auto", "vec", "tma"])
+    ap.add_argument("--e2e-calls", type=int, default=3)
+    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.steps < 1:
+        raise SystemExit("--steps must be >= 1")
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

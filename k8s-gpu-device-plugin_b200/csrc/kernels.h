@@ -1,0 +1,49 @@
+// kernels.h — host-callable launchers for the probe kernels.  Every launcher
+// only enqueues on `stream`; none allocates, synchronises or touches the host.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gpuprobe.h"
+
+namespace gp {
+
+// internal pattern kind: checksum only, no expected value (mismatches stay 0)
+constexpr int kPatNone = 3;
+
+// per-block partial of a verify launch (scratch memory; see pattern.cu)
+struct VerifyPartial {
+  uint64_t sum, xor_, wsum, mismatches, first_bad_index, first_bad_xor;
+};
+constexpr int kMaxVerifyBlocks = 4096;
+// scratch layout: [kMaxVerifyBlocks] VerifyPartial, then one uint32 ticket (zero at rest)
+constexpr size_t kVerifyScratchBytes = kMaxVerifyBlocks * sizeof(VerifyPartial) + 256;
+
+struct LaunchGeom {
+  int sm_count;
+};
+
+cudaError_t launch_pattern_fill(uint64_t* words, uint64_t nwords, int kind, int pass, int sm_count,
+                                cudaStream_t stream);
+// result is fully overwritten by plain stores of the last block; scratch must be
+// kVerifyScratchBytes with the ticket word zero (it is left zero on completion).
+cudaError_t launch_pattern_verify(const uint64_t* words, uint64_t nwords, int kind, int pass,
+                                  void* scratch, gp_pattern_result* d_result, int sm_count,
+                                  cudaStream_t stream);
+cudaError_t launch_bitflip(uint64_t* words, uint64_t word_index, int bit, cudaStream_t stream);
+
+// HBM stream kernels.  bytes is a multiple of 1 MiB; variant is GP_STREAM_VEC or GP_STREAM_TMA.
+cudaError_t launch_copy(void* dst, const void* src, uint64_t bytes, int variant, int sm_count,
+                        cudaStream_t stream);
+cudaError_t launch_triad(float* a, const float* b, const float* c, float s, uint64_t bytes,
+                         int variant, int sm_count, cudaStream_t stream);
+// operand generators (GP_K_INIT)
+cudaError_t launch_gen_f32(float* dst, uint64_t n, uint64_t seed, int sm_count, cudaStream_t stream);
+cudaError_t launch_gen_bf16(uint16_t* dst, uint64_t n, uint64_t seed, int sm_count,
+                            cudaStream_t stream);
+// counts fp32 elements of a that differ bitwise from fmaf(s, gen(c), gen(b)); *d_count += count
+cudaError_t launch_triad_check(const float* a, uint64_t n, uint64_t seed, float s,
+                               unsigned long long* d_count, int sm_count, cudaStream_t stream);
+cudaError_t stream_kernels_configure();  // opt-in dynamic smem; call once per device
+
+}  // namespace gp
