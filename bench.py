@@ -234,31 +234,45 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         wall_max, dev_ms_max = float(t[0]), float(t[1])
 
-    # ---- e2e: the call the plugin makes (gp_probe_device), cold arena, results to host -----
-    probe.close()
-    e2e_calls = max(1, min(args.steps, args.e2e_calls))
-    mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_TRIAD | gpuprobe.GP_PROBE_PATTERN
-    p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
-    p2.probe_device(dev, mask)  # warm-up call (context, module load)
-    p2.kernel_stats(dev, reset=True)
-    barrier()
-    t0 = time.perf_counter()
-    last = None
-    for _ in range(e2e_calls):
-        last = p2.probe_device(dev, mask)   # malloc arena, generate, warm up, time, verify, D2H, free
-        if not last.healthy:
-            raise SystemExit(f"e2e: gp_probe_device verdict unhealthy, failed_mask={last.failed_mask}")
-    barrier()
-    e2e_wall = time.perf_counter() - t0
-    st2 = p2.kernel_stats(dev)
-    e2e_bytes = sum(st2[i].algo_bytes for i in (gpuprobe.GP_K_COPY, gpuprobe.GP_K_TRIAD,
-                                                gpuprobe.GP_K_FILL, gpuprobe.GP_K_VERIFY))
-    e2e_launches = sum(int(st2[i].launches) for i in range(7))
-    if dist is not None:
-        t = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_wall = float(t[0])
-    d2h = ctypes.sizeof(gpuprobe.DeviceResult) + last.pattern_passes * 48 + 48 + 8
+    e2e = None
+    if args.no_e2e:
+        probe.close()
+        p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
+    else:
+        # ---- e2e: the call the plugin makes (gp_probe_device), cold arena, results to host -----
+        probe.close()
+        e2e_calls = max(1, min(args.steps, args.e2e_calls))
+        mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_TRIAD | gpuprobe.GP_PROBE_PATTERN
+        p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
+        p2.probe_device(dev, mask)  # warm-up call (context, module load)
+        p2.kernel_stats(dev, reset=True)
+        barrier()
+        t0 = time.perf_counter()
+        last = None
+        for _ in range(e2e_calls):
+            last = p2.probe_device(dev, mask)   # malloc arena, generate, warm up, time, verify, D2H, free
+            if not last.healthy:
+                raise SystemExit(f"e2e: gp_probe_device verdict unhealthy, failed_mask={last.failed_mask}")
+        barrier()
+        e2e_wall = time.perf_counter() - t0
+        st2 = p2.kernel_stats(dev)
+        e2e_bytes = sum(st2[i].algo_bytes for i in (gpuprobe.GP_K_COPY, gpuprobe.GP_K_TRIAD,
+                                                    gpuprobe.GP_K_FILL, gpuprobe.GP_K_VERIFY))
+        e2e_launches = sum(int(st2[i].launches) for i in range(7))
+        if dist is not None:
+            t = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_wall = float(t[0])
+        d2h = ctypes.sizeof(gpuprobe.DeviceResult) + last.pattern_passes * 48 + 48 + 8
+        e2e = {"value": e2e_bytes * n_gpus / e2e_wall / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h,
+               "calls": e2e_calls, "seconds_per_call": e2e_wall / e2e_calls,
+               "launches_per_call": e2e_launches // e2e_calls,
+               "what": "gp_probe_device(uuid, COPY|TRIAD|PATTERN) through the C ABI with a cold arena: "
+                       "cudaMalloc, operand generation, warm-up + timed launches, 64+2 fill/verify "
+                       "passes, verification, results copied to the caller's host struct, cudaFree. "
+                       "The probe takes no bulk host input by construction (patterns are generated "
+                       "on the device it grades), so h2d is 0 and d2h is the result bytes."}
 
     # ---- full-box sweep seconds (second half of the metric), rank 0, all N GPUs, one process --
     sweep = None
@@ -337,15 +351,7 @@ def run_ours(args):
         "per_gpu_gbps": value / n_gpus, "frac_of_8tbps_per_gpu": value / n_gpus / 8000.0,
         "device_ms_per_step": dev_ms_max / args.steps,
         "roofline": roofline, "kernels": kernels, "clocks": clocks,
-        "e2e": {"value": e2e_bytes * n_gpus / e2e_wall / 1e9, "unit": UNIT,
-                "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h,
-                "calls": e2e_calls, "seconds_per_call": e2e_wall / e2e_calls,
-                "launches_per_call": e2e_launches // e2e_calls,
-                "what": "gp_probe_device(uuid, COPY|TRIAD|PATTERN) through the C ABI with a cold arena: "
-                        "cudaMalloc, operand generation, warm-up + timed launches, 64+2 fill/verify "
-                        "passes, verification, results copied to the caller's host struct, cudaFree. "
-                        "The probe takes no bulk host input by construction (patterns are generated "
-                        "on the device it grades), so h2d is 0 and d2h is the result bytes."},
+        "e2e": e2e,
         "gpu_launches": gpu_launches,
     }
     if sweep is not None:
@@ -373,6 +379,7 @@ def main():
     ap.add_argument("--variant", default="auto", choices=["auto", "vec", "tma"])
     ap.add_argument("--e2e-calls", type=int, default=3)
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the e2e leg")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.steps < 1:

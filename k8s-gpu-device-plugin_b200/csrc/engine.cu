@@ -91,6 +91,7 @@ int device_prepare(Ctx* ctx, Device* d) {
       kVerifyScratchBytes + kMaxResults * sizeof(gp_pattern_result) + 256;
   CU_OR_RETURN(cudaMalloc(&d->scratch, scratch_bytes), nullptr);
   CU_OR_RETURN(cudaMemsetAsync(d->scratch, 0, scratch_bytes, d->stream), nullptr);
+  CU_OR_RETURN(launch_verify_scratch_init(d->scratch, d->stream), nullptr);
   d->d_results = reinterpret_cast<gp_pattern_result*>(d->scratch + kVerifyScratchBytes);
   d->d_count = reinterpret_cast<unsigned long long*>(d->scratch + kVerifyScratchBytes +
                                                      kMaxResults * sizeof(gp_pattern_result));

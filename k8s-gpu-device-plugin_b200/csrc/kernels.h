@@ -11,13 +11,17 @@ namespace gp {
 // internal pattern kind: checksum only, no expected value (mismatches stay 0)
 constexpr int kPatNone = 3;
 
-// per-block partial of a verify launch (scratch memory; see pattern.cu)
-struct VerifyPartial {
-  uint64_t sum, xor_, wsum, mismatches, first_bad_index, first_bad_xor;
+// accumulator slot of a verify launch (scratch memory; see pattern.cu).  CTAs add their
+// partials into slot (blockIdx & (kVerifySlots-1)); 64-byte stride keeps slots in separate
+// L2 sectors so the reductions spread over the L2 slices.
+struct VerifySlot {
+  uint64_t sum, xor_, wsum, mismatches, first_bad_index;
+  uint64_t pad[3];
 };
-constexpr int kMaxVerifyBlocks = 4096;
-// scratch layout: [kMaxVerifyBlocks] VerifyPartial, then one uint32 ticket (zero at rest)
-constexpr size_t kVerifyScratchBytes = kMaxVerifyBlocks * sizeof(VerifyPartial) + 256;
+constexpr int kVerifySlots = 512;
+// scratch layout: [kVerifySlots] VerifySlot.  Rest state: sums 0, first_bad_index all-ones
+// (set once by launch_verify_scratch_init, restored by every verify launch's finalize CTA).
+constexpr size_t kVerifyScratchBytes = kVerifySlots * sizeof(VerifySlot) + 256;
 
 struct LaunchGeom {
   int sm_count;
@@ -25,8 +29,10 @@ struct LaunchGeom {
 
 cudaError_t launch_pattern_fill(uint64_t* words, uint64_t nwords, int kind, int pass, int sm_count,
                                 cudaStream_t stream);
-// result is fully overwritten by plain stores of the last block; scratch must be
-// kVerifyScratchBytes with the ticket word zero (it is left zero on completion).
+cudaError_t launch_verify_scratch_init(void* scratch, cudaStream_t stream);
+// two launches: the chunk grid, then a one-CTA finalize.  result is fully overwritten by plain
+// stores of the finalize CTA; scratch must be
+// kVerifyScratchBytes in its rest state (it is left in that state on completion).
 cudaError_t launch_pattern_verify(const uint64_t* words, uint64_t nwords, int kind, int pass,
                                   void* scratch, gp_pattern_result* d_result, int sm_count,
                                   cudaStream_t stream);

@@ -4,85 +4,89 @@
 // looking at the device); the arithmetic is the spec of SURVEY.md §8(c) and
 // must be bit-exact against oracle/gpuprobe_oracle.c.
 //
-// Both kernels are HBM-bound integer work: 256-bit accesses, a persistent grid
-// of sm_count * kBlocksPerSm CTAs walking the arena with a grid stride so that
-// neighbouring CTAs touch neighbouring DRAM pages at the same time.
+// Both kernels are HBM-bound integer work: 256-bit accesses (LDG/STG.E.256),
+// one CTA per contiguous 32 KiB chunk.
 //   fill   : N bytes written, nothing read.
 //   verify : N bytes read; sum / xor / position-weighted sum (all mod 2^64, so
 //            reduction order is irrelevant), mismatch count, first bad index and
-//            its xor.  Warp-shuffle reduction -> one partial per CTA in scratch
-//            -> the last CTA to finish (ticket counter) folds the partials and
-//            writes the 48-byte result with plain stores.  The ticket returns to
-//            zero, so back-to-back launches need no memset and no atomics on
-//            the result.
+//            its xor.  Uses kVerifyScratchBytes of scratch (accumulator slots),
+//            left in its rest state by every launch.
 #include "common.cuh"
 #include "kernels.h"
 
 namespace gp {
 
+// Launch shape, measured with tools/hbm_sweep.cu on B200 (profiles/hbm_sweep_r01.txt):
+// a NON-persistent grid of one CTA per contiguous 32 KiB chunk lets the hardware CTA
+// dispatcher sweep a tight, linearly advancing window over DRAM: 7.60 TB/s fill and
+// 7.59 TB/s read, against 6.35 / 7.38 TB/s for a persistent grid-stride grid of the same
+// instructions.  Every thread issues its four 256-bit accesses up front, no loop.
 constexpr int kThreads = 256;
-
-// Persistent grids: exactly as many CTAs as fit at once (one wave), asked of the
-// occupancy calculator per kernel so a register-count change cannot create a tail wave.
-template <auto kernel>
-static int resident_blocks_per_sm() {
-  static int cached = 0;
-  if (cached == 0) {
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) n = 1;
-    cached = n;
-  }
-  return cached;
-}
+constexpr int kVecPerThread = 4;
+constexpr uint64_t kChunkVec = (uint64_t)kThreads * kVecPerThread;  // 1024 x 32 B = 32 KiB per CTA
 
 template <int KIND>
 __global__ void __launch_bounds__(kThreads)
 pattern_fill_kernel(uint64_t* __restrict__ words, uint64_t nvec, int pass) {
-  const uint64_t stride = (uint64_t)gridDim.x * kThreads;
-  for (uint64_t g = (uint64_t)blockIdx.x * kThreads + threadIdx.x; g < nvec; g += stride) {
-    const uint64_t i = g << 2;
-    u64x4 v;
+  const uint64_t g0 = (uint64_t)blockIdx.x * kChunkVec + threadIdx.x;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) v.v[j] = pattern_word<KIND>(pass, i + j);
-    st256_stream(words + i, v);
+  for (int u = 0; u < kVecPerThread; ++u) {
+    const uint64_t g = g0 + (uint64_t)u * kThreads;
+    if (g < nvec) {
+      const uint64_t i = g << 2;
+      u64x4 v;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v.v[j] = pattern_word<KIND>(pass, i + j);
+      st256_stream(words + i, v);
+    }
   }
 }
 
 struct Acc {
-  uint64_t sum, xr, wsum, mism, first_idx, first_xor;
+  uint64_t sum, xr, wsum, mism, first_idx;
 };
 
 __device__ __forceinline__ void acc_init(Acc& a) {
-  a.sum = 0; a.xr = 0; a.wsum = 0; a.mism = 0; a.first_idx = ~0ull; a.first_xor = 0;
+  a.sum = 0; a.xr = 0; a.wsum = 0; a.mism = 0; a.first_idx = ~0ull;
 }
 
+// word-by-word compare of one vector; only reached when the vector is known to differ (or on
+// the ragged last chunk).  Everything travels in registers so the caller's vectors never get
+// a stack home: returns the lowest bad word index (all-ones if none) and adds to *count.
+template <int KIND>
+__device__ __noinline__ uint64_t compare_words_slow(uint64_t w0, uint64_t w1, uint64_t w2,
+                                                    uint64_t w3, uint64_t i, int pass,
+                                                    uint32_t& count) {
+  uint64_t first = ~0ull;
+  const uint64_t w[4] = {w0, w1, w2, w3};
+#pragma unroll
+  for (int j = 3; j >= 0; --j) {
+    if (w[j] != pattern_word<KIND>(pass, i + j)) { first = i + j; ++count; }
+  }
+  return first;
+}
+template <int KIND>
+__device__ __forceinline__ void compare_vec_slow(Acc& a, const u64x4& v, uint64_t g, int pass) {
+  uint32_t count = 0;
+  const uint64_t first = compare_words_slow<KIND>(v.v[0], v.v[1], v.v[2], v.v[3], g << 2, pass, count);
+  if (first < a.first_idx) a.first_idx = first;
+  a.mism += count;
+}
+
+// generic single-vector accumulate (ragged last chunk only)
 template <int KIND>
 __device__ __forceinline__ void acc_vec(Acc& a, const u64x4& v, uint64_t g, int pass) {
   const uint64_t i = g << 2;
   const uint64_t s4 = (v.v[0] + v.v[1]) + (v.v[2] + v.v[3]);
   a.sum += s4;
   a.xr ^= (v.v[0] ^ v.v[1]) ^ (v.v[2] ^ v.v[3]);
-  // SUM_j w_j (2(i+j)+1) = (2i+1) s4 + 2 (w1 + 2 w2 + 3 w3): one 64-bit multiply per vector
   a.wsum += (2 * i + 1) * s4 + 2 * (v.v[1] + 2 * v.v[2] + 3 * v.v[3]);
-  if constexpr (KIND != kPatNone) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint64_t e = pattern_word<KIND>(pass, i + j);
-      if (v.v[j] != e) {  // cold path
-        if (a.mism == 0) { a.first_idx = i + j; a.first_xor = v.v[j] ^ e; }
-        ++a.mism;
-      }
-    }
-  }
+  if constexpr (KIND != kPatNone) compare_vec_slow<KIND>(a, v, g, pass);
 }
 
-__device__ __forceinline__ void acc_merge_first(Acc& a, uint64_t idx, uint64_t x) {
-  if (idx < a.first_idx) { a.first_idx = idx; a.first_xor = x; }
-}
-
-// Reduce across the CTA; the result is valid in thread 0.
+// Reduce across the CTA (finalize kernel only); the result is valid in thread 0.
 __device__ __forceinline__ void block_reduce(Acc& a) {
-  __shared__ uint64_t sh[kThreads / 32][6];
+  __shared__ uint64_t sh[kThreads / 32][5];
   a.sum = warp_sum_u64(a.sum);
   a.xr = warp_xor_u64(a.xr);
   a.wsum = warp_sum_u64(a.wsum);
@@ -90,105 +94,171 @@ __device__ __forceinline__ void block_reduce(Acc& a) {
 #pragma unroll
   for (int m = 16; m > 0; m >>= 1) {
     const uint64_t oi = shfl_xor_u64(a.first_idx, m);
-    const uint64_t ox = shfl_xor_u64(a.first_xor, m);
-    acc_merge_first(a, oi, ox);
+    if (oi < a.first_idx) a.first_idx = oi;
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  __syncthreads();  // sh may still be read by a previous call
   if (lane == 0) {
     sh[warp][0] = a.sum; sh[warp][1] = a.xr; sh[warp][2] = a.wsum;
-    sh[warp][3] = a.mism; sh[warp][4] = a.first_idx; sh[warp][5] = a.first_xor;
+    sh[warp][3] = a.mism; sh[warp][4] = a.first_idx;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int w = 1; w < kThreads / 32; ++w) {
       a.sum += sh[w][0]; a.xr ^= sh[w][1]; a.wsum += sh[w][2]; a.mism += sh[w][3];
-      acc_merge_first(a, sh[w][4], sh[w][5]);
+      if (sh[w][4] < a.first_idx) a.first_idx = sh[w][4];
+    }
+  }
+}
+
+// verify: N bytes read.  The kernel is close to issue-bound on the integer pipes (an earlier
+// word-at-a-time version reached 6.1–6.5 TB/s while a bare read reaches 7.6), so the inner
+// loop is built from per-thread invariants:
+//   * a thread's vectors are 256 vectors = 1024 words apart, a multiple of 64 words, so its
+//     four expected walking-ones words are the same for every vector: one xor/or tree and one
+//     branch per 256-bit vector;
+//   * address words of a vector share their upper bits: e_j = 32 g | 8 j;
+//   * SUM_i w_i (2i+1) over the thread's vectors needs ONE 64-bit multiply:
+//       (8 g0 + 1) S + 2048 SUM_u u s4_u + 2 (A1 + 2 A2 + 3 A3),  A_j = SUM_u w_{u,j}.
+// Each warp folds its partial with shuffles and lane 0 adds it into one of kVerifySlots
+// accumulator slots in scratch memory with fire-and-forget reductions (RED.ADD / RED.XOR /
+// RED.MIN at L2; all arithmetic is mod 2^64, so the order is irrelevant and the result
+// bit-exact).  No CTA waits on anything: a first version elected the last CTA with a returning
+// ticket atomic and lost 20 % of the bandwidth to that one hot address.  A one-CTA finalize
+// launch on the same stream folds the slots, looks up the xor at the first bad index, writes
+// the 48-byte result with plain stores and returns the slots to their rest state — so verify
+// launches chain on a stream with no memset in between.
+template <int KIND>
+__global__ void __launch_bounds__(kThreads)
+pattern_verify_kernel(const uint64_t* __restrict__ words, uint64_t nvec, int pass,
+                      VerifySlot* __restrict__ slots) {
+  Acc a;
+  acc_init(a);
+  const uint64_t g0 = (uint64_t)blockIdx.x * kChunkVec + threadIdx.x;
+  if (g0 - threadIdx.x + kChunkVec <= nvec) {  // whole chunk: every load issued up front
+    u64x4 v[kVecPerThread];
+#pragma unroll
+    for (int u = 0; u < kVecPerThread; ++u) v[u] = ld256_stream(words + ((g0 + (uint64_t)u * kThreads) << 2));
+    uint64_t R = 0, B = 0, A1 = 0, A2 = 0, A3 = 0, X = 0, S = 0;
+#pragma unroll
+    for (int u = kVecPerThread - 1; u >= 0; --u) {
+      const uint64_t s4 = (v[u].v[0] + v[u].v[1]) + (v[u].v[2] + v[u].v[3]);
+      X ^= (v[u].v[0] ^ v[u].v[1]) ^ (v[u].v[2] ^ v[u].v[3]);
+      A1 += v[u].v[1]; A2 += v[u].v[2]; A3 += v[u].v[3];
+      if (u > 0) { R += s4; B += R; } else { S = R + s4; }
+    }
+    a.sum = S;
+    a.xr = X;
+    a.wsum = (8 * g0 + 1) * S + (uint64_t)(8 * kThreads) * B + 2 * (A1 + 2 * A2 + 3 * A3);
+    if constexpr (KIND == GP_PAT_WALKING_ONES || KIND == GP_PAT_WALKING_ZEROS) {
+      uint64_t e[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) e[j] = pattern_word<KIND>(pass, (g0 << 2) + j);  // same for every u
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u) {
+        const uint64_t m = ((v[u].v[0] ^ e[0]) | (v[u].v[1] ^ e[1])) | ((v[u].v[2] ^ e[2]) | (v[u].v[3] ^ e[3]));
+        if (m) compare_vec_slow<KIND>(a, v[u], g0 + (uint64_t)u * kThreads, pass);
+      }
+    } else if constexpr (KIND == GP_PAT_ADDRESS) {
+      const uint64_t inv = (pass & 1) ? ~0ull : 0ull;
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u) {
+        const uint64_t e0 = ((g0 + (uint64_t)u * kThreads) << 5) ^ inv;  // 8 * (4 g) ; low five bits free
+        const uint64_t m = ((v[u].v[0] ^ e0) | (v[u].v[1] ^ e0 ^ 8)) | ((v[u].v[2] ^ e0 ^ 16) | (v[u].v[3] ^ e0 ^ 24));
+        if (m) compare_vec_slow<KIND>(a, v[u], g0 + (uint64_t)u * kThreads, pass);
+      }
+    }
+  } else {  // ragged last chunk
+    for (int u = 0; u < kVecPerThread; ++u) {
+      const uint64_t g = g0 + (uint64_t)u * kThreads;
+      if (g < nvec) acc_vec<KIND>(a, ld256_stream(words + (g << 2)), g, pass);
+    }
+  }
+  a.sum = warp_sum_u64(a.sum);
+  a.xr = warp_xor_u64(a.xr);
+  a.wsum = warp_sum_u64(a.wsum);
+  const bool any_bad = __any_sync(0xffffffffu, a.mism != 0);
+  if (any_bad) {  // cold
+    a.mism = warp_sum_u64(a.mism);
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+      const uint64_t oi = shfl_xor_u64(a.first_idx, m);
+      if (oi < a.first_idx) a.first_idx = oi;
+    }
+  }
+  if ((threadIdx.x & 31) == 0) {
+    VerifySlot* s = slots + ((blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5)) & (kVerifySlots - 1));
+    atomicAdd(reinterpret_cast<unsigned long long*>(&s->sum), (unsigned long long)a.sum);
+    atomicXor(reinterpret_cast<unsigned long long*>(&s->xor_), (unsigned long long)a.xr);
+    atomicAdd(reinterpret_cast<unsigned long long*>(&s->wsum), (unsigned long long)a.wsum);
+    if (any_bad) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(&s->mismatches), (unsigned long long)a.mism);
+      atomicMin(reinterpret_cast<unsigned long long*>(&s->first_bad_index), (unsigned long long)a.first_idx);
     }
   }
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(kThreads, 4)
-pattern_verify_kernel(const uint64_t* __restrict__ words, uint64_t nvec, int pass,
-                      VerifyPartial* __restrict__ partials, unsigned int* __restrict__ ticket,
-                      gp_pattern_result* __restrict__ result) {
+__global__ void __launch_bounds__(kThreads)
+pattern_verify_finalize_kernel(const uint64_t* __restrict__ words, int pass,
+                               VerifySlot* __restrict__ slots,
+                               gp_pattern_result* __restrict__ result) {
   Acc a;
   acc_init(a);
-  const uint64_t stride = (uint64_t)gridDim.x * kThreads;
-  uint64_t g = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
-  // four independent 256-bit loads in flight per thread
-  for (; g + 3 * stride < nvec; g += 4 * stride) {
-    const u64x4 v0 = ld256_stream(words + (g << 2));
-    const u64x4 v1 = ld256_stream(words + ((g + stride) << 2));
-    const u64x4 v2 = ld256_stream(words + ((g + 2 * stride) << 2));
-    const u64x4 v3 = ld256_stream(words + ((g + 3 * stride) << 2));
-    acc_vec<KIND>(a, v0, g, pass);
-    acc_vec<KIND>(a, v1, g + stride, pass);
-    acc_vec<KIND>(a, v2, g + 2 * stride, pass);
-    acc_vec<KIND>(a, v3, g + 3 * stride, pass);
-  }
-  for (; g < nvec; g += stride) {
-    const u64x4 v = ld256_stream(words + (g << 2));
-    acc_vec<KIND>(a, v, g, pass);
-  }
-  block_reduce(a);
-
-  __shared__ bool is_last;
-  if (threadIdx.x == 0) {
-    VerifyPartial p{a.sum, a.xr, a.wsum, a.mism, a.first_idx, a.first_xor};
-    partials[blockIdx.x] = p;
-    __threadfence();
-    const unsigned int t = atomicAdd(ticket, 1u);
-    is_last = (t == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  acc_init(a);
-  for (unsigned int b = threadIdx.x; b < gridDim.x; b += kThreads) {
-    const volatile VerifyPartial* p = partials + b;
-    a.sum += p->sum; a.xr ^= p->xor_; a.wsum += p->wsum; a.mism += p->mismatches;
-    acc_merge_first(a, p->first_bad_index, p->first_bad_xor);
+  for (int b = threadIdx.x; b < kVerifySlots; b += kThreads) {
+    VerifySlot* s = slots + b;
+    a.sum += s->sum; a.xr ^= s->xor_; a.wsum += s->wsum; a.mism += s->mismatches;
+    if (s->first_bad_index < a.first_idx) a.first_idx = s->first_bad_index;
+    s->sum = 0; s->xor_ = 0; s->wsum = 0; s->mismatches = 0; s->first_bad_index = ~0ull;  // rest state
   }
   block_reduce(a);
   if (threadIdx.x == 0) {
     gp_pattern_result r;
     r.sum = a.sum; r.xor_ = a.xr; r.wsum = a.wsum; r.mismatches = a.mism;
-    r.first_bad_index = a.first_idx; r.first_bad_xor = a.first_xor;
+    r.first_bad_index = a.first_idx;
+    r.first_bad_xor = 0;
+    if constexpr (KIND != kPatNone) {
+      if (a.first_idx != ~0ull) r.first_bad_xor = words[a.first_idx] ^ pattern_word<KIND>(pass, a.first_idx);
+    }
     *result = r;
-    *ticket = 0;  // at rest for the next launch on this stream
   }
 }
 
-// A handful of trailing words (nwords % 4) never occurs: the ABI requires
-// nwords % 64 == 0, checked in the engine.
+__global__ void verify_scratch_init_kernel(VerifySlot* slots) {
+  for (int b = threadIdx.x; b < kVerifySlots; b += blockDim.x) {
+    slots[b].sum = 0; slots[b].xor_ = 0; slots[b].wsum = 0; slots[b].mismatches = 0;
+    slots[b].first_bad_index = ~0ull; slots[b].pad[0] = slots[b].pad[1] = slots[b].pad[2] = 0;
+  }
+}
 
-static int grid_for(uint64_t nvec, int sm_count, int blocks_per_sm) {
-  uint64_t want = (nvec + kThreads - 1) / kThreads;
-  uint64_t cap = (uint64_t)sm_count * blocks_per_sm;
-  if (cap > (uint64_t)kMaxVerifyBlocks) cap = kMaxVerifyBlocks;
-  if (want > cap) want = cap;
-  if (want < 1) want = 1;
-  return (int)want;
+cudaError_t launch_verify_scratch_init(void* scratch, cudaStream_t stream) {
+  verify_scratch_init_kernel<<<1, 256, 0, stream>>>(reinterpret_cast<VerifySlot*>(scratch));
+  return cudaGetLastError();
+}
+
+// The ABI requires nwords % 64 == 0, so nwords is always a whole number of
+// 256-bit vectors; the engine checks it.
+static unsigned int grid_for(uint64_t nvec) {
+  const uint64_t g = (nvec + kChunkVec - 1) / kChunkVec;
+  return (unsigned int)(g < 1 ? 1 : g);
 }
 
 cudaError_t launch_pattern_fill(uint64_t* words, uint64_t nwords, int kind, int pass, int sm_count,
                                 cudaStream_t stream) {
+  (void)sm_count;
   const uint64_t nvec = nwords >> 2;
   if (nvec == 0) return cudaSuccess;
-#define GP_FILL_CASE(K)                                                              \
-  case K: {                                                                          \
-    const int grid = grid_for(nvec, sm_count, resident_blocks_per_sm<pattern_fill_kernel<K>>()); \
-    pattern_fill_kernel<K><<<grid, kThreads, 0, stream>>>(words, nvec, pass);        \
-    break;                                                                           \
-  }
+  const unsigned int grid = grid_for(nvec);
   switch (kind) {
-    GP_FILL_CASE(GP_PAT_WALKING_ONES)
-    GP_FILL_CASE(GP_PAT_WALKING_ZEROS)
-    GP_FILL_CASE(GP_PAT_ADDRESS)
-#undef GP_FILL_CASE
+    case GP_PAT_WALKING_ONES:
+      pattern_fill_kernel<GP_PAT_WALKING_ONES><<<grid, kThreads, 0, stream>>>(words, nvec, pass);
+      break;
+    case GP_PAT_WALKING_ZEROS:
+      pattern_fill_kernel<GP_PAT_WALKING_ZEROS><<<grid, kThreads, 0, stream>>>(words, nvec, pass);
+      break;
+    case GP_PAT_ADDRESS:
+      pattern_fill_kernel<GP_PAT_ADDRESS><<<grid, kThreads, 0, stream>>>(words, nvec, pass);
+      break;
     default:
       return cudaErrorInvalidValue;
   }
@@ -198,16 +268,15 @@ cudaError_t launch_pattern_fill(uint64_t* words, uint64_t nwords, int kind, int 
 cudaError_t launch_pattern_verify(const uint64_t* words, uint64_t nwords, int kind, int pass,
                                   void* scratch, gp_pattern_result* d_result, int sm_count,
                                   cudaStream_t stream) {
+  (void)sm_count;
   const uint64_t nvec = nwords >> 2;
-  VerifyPartial* partials = reinterpret_cast<VerifyPartial*>(scratch);
-  unsigned int* ticket = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(scratch) +
-                                                         kMaxVerifyBlocks * sizeof(VerifyPartial));
-#define GP_VERIFY_CASE(K)                                                              \
-  case K: {                                                                            \
-    const int grid = grid_for(nvec, sm_count, resident_blocks_per_sm<pattern_verify_kernel<K>>()); \
-    pattern_verify_kernel<K><<<grid, kThreads, 0, stream>>>(words, nvec, pass, partials, ticket, d_result); \
-    break;                                                                             \
-  }
+  const unsigned int grid = grid_for(nvec);
+  VerifySlot* slots = reinterpret_cast<VerifySlot*>(scratch);
+#define GP_VERIFY_CASE(K)                                                                        \
+  case K:                                                                                        \
+    if (nvec) pattern_verify_kernel<K><<<grid, kThreads, 0, stream>>>(words, nvec, pass, slots); \
+    pattern_verify_finalize_kernel<K><<<1, kThreads, 0, stream>>>(words, pass, slots, d_result); \
+    break;
   switch (kind) {
     GP_VERIFY_CASE(GP_PAT_WALKING_ONES)
     GP_VERIFY_CASE(GP_PAT_WALKING_ZEROS)

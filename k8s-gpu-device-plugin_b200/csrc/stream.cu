@@ -4,39 +4,45 @@
 // runtime, it moves no device memory).  Algorithmic bytes per launch
 // (SURVEY.md §8d): copy 2N, triad 3N, N = bytes per array.
 //
-// Two hand-written variants of each, selected by gp_config.stream_variant:
-//   VEC : persistent grid, four 256-bit loads in flight per thread, then four
-//         256-bit stores (LDG.E.256 / STG.E.256, L1 no-allocate).
-//   TMA : one CTA per SM.  A producer thread streams 32 KiB tiles
-//         global->shared with cp.async.bulk (UBLKCP) completing on an
-//         mbarrier ring; copy drains each tile shared->global with
-//         cp.async.bulk from the same thread (no thread ever touches the
-//         data); triad lets four consumer warps combine the b and c tiles in
-//         place in shared memory (LDS.128/STS.128), fences the generic proxy
-//         against the async proxy and bulk-stores the result tile.
+// Two hand-written variants of each, selected by gp_config.stream_variant, both
+// launched as NON-persistent grids of one CTA per contiguous chunk (see the note
+// at kCopyVecPerThread):
+//   VEC : every thread issues its 256-bit loads, then its 256-bit stores
+//         (LDG.E.256 / STG.E.256, L1 no-allocate).
+//   TMA : cp.async.bulk global->shared (UBLKCP) completing on mbarriers and
+//         cp.async.bulk shared->global; copy never touches the data with a
+//         thread, triad combines the b and c tiles in place in shared memory.
+// On B200 the two are within noise of each other (copy 6.93 vs 6.95 TB/s, triad
+// 7.08 vs 7.08 TB/s, profiles/hbm_sweep_r01.txt); AUTO picks TMA.
 #include "common.cuh"
 #include "kernels.h"
 
 namespace gp {
 
 constexpr int kVecThreads = 256;
+// Launch shape measured with tools/hbm_sweep.cu (profiles/hbm_sweep_r01.txt): one CTA per
+// contiguous chunk, no loop, all loads of a thread issued before its stores.  The hardware
+// CTA dispatcher then sweeps a tight window over DRAM: copy 6.95 TB/s against 6.2–6.6 TB/s
+// for persistent grid-stride grids and 6.57 TB/s for cudaMemcpyAsync.
+constexpr int kCopyVecPerThread = 4;  // 32 KiB per CTA
+constexpr int kTriVecPerThread = 2;   // 16 KiB of each array per CTA
 
 // ---------------------------------------------------------------- VEC copy --
 __global__ void __launch_bounds__(kVecThreads)
 copy_vec_kernel(const u64x4* __restrict__ src, u64x4* __restrict__ dst, uint64_t nvec) {
-  const uint64_t stride = (uint64_t)gridDim.x * kVecThreads;
-  uint64_t g = (uint64_t)blockIdx.x * kVecThreads + threadIdx.x;
-  for (; g + 3 * stride < nvec; g += 4 * stride) {
-    const u64x4 v0 = ld256_stream(src + g);
-    const u64x4 v1 = ld256_stream(src + g + stride);
-    const u64x4 v2 = ld256_stream(src + g + 2 * stride);
-    const u64x4 v3 = ld256_stream(src + g + 3 * stride);
-    st256_stream(dst + g, v0);
-    st256_stream(dst + g + stride, v1);
-    st256_stream(dst + g + 2 * stride, v2);
-    st256_stream(dst + g + 3 * stride, v3);
+  const uint64_t g0 = (uint64_t)blockIdx.x * (kVecThreads * kCopyVecPerThread) + threadIdx.x;
+  if (g0 - threadIdx.x + kVecThreads * kCopyVecPerThread <= nvec) {
+    u64x4 v[kCopyVecPerThread];
+#pragma unroll
+    for (int u = 0; u < kCopyVecPerThread; ++u) v[u] = ld256_stream(src + g0 + u * kVecThreads);
+#pragma unroll
+    for (int u = 0; u < kCopyVecPerThread; ++u) st256_stream(dst + g0 + u * kVecThreads, v[u]);
+  } else {
+    for (int u = 0; u < kCopyVecPerThread; ++u) {
+      const uint64_t g = g0 + (uint64_t)u * kVecThreads;
+      if (g < nvec) st256_stream(dst + g, ld256_stream(src + g));
+    }
   }
-  for (; g < nvec; g += stride) st256_stream(dst + g, ld256_stream(src + g));
 }
 
 // --------------------------------------------------------------- VEC triad --
@@ -67,118 +73,99 @@ __device__ __forceinline__ f32x8 triad8(const f32x8& b, const f32x8& c, float s)
 __global__ void __launch_bounds__(kVecThreads)
 triad_vec_kernel(f32x8* __restrict__ a, const f32x8* __restrict__ b, const f32x8* __restrict__ c,
                  float s, uint64_t nvec) {
-  const uint64_t stride = (uint64_t)gridDim.x * kVecThreads;
-  uint64_t g = (uint64_t)blockIdx.x * kVecThreads + threadIdx.x;
-  for (; g + stride < nvec; g += 2 * stride) {
-    const f32x8 b0 = ld256_f(b + g), c0 = ld256_f(c + g);
-    const f32x8 b1 = ld256_f(b + g + stride), c1 = ld256_f(c + g + stride);
-    st256_f(a + g, triad8(b0, c0, s));
-    st256_f(a + g + stride, triad8(b1, c1, s));
+  const uint64_t g0 = (uint64_t)blockIdx.x * (kVecThreads * kTriVecPerThread) + threadIdx.x;
+  if (g0 - threadIdx.x + kVecThreads * kTriVecPerThread <= nvec) {
+    f32x8 bv[kTriVecPerThread], cv[kTriVecPerThread];
+#pragma unroll
+    for (int u = 0; u < kTriVecPerThread; ++u) {
+      bv[u] = ld256_f(b + g0 + u * kVecThreads);
+      cv[u] = ld256_f(c + g0 + u * kVecThreads);
+    }
+#pragma unroll
+    for (int u = 0; u < kTriVecPerThread; ++u) st256_f(a + g0 + u * kVecThreads, triad8(bv[u], cv[u], s));
+  } else {
+    for (int u = 0; u < kTriVecPerThread; ++u) {
+      const uint64_t g = g0 + (uint64_t)u * kVecThreads;
+      if (g < nvec) st256_f(a + g, triad8(ld256_f(b + g), ld256_f(c + g), s));
+    }
   }
-  for (; g < nvec; g += stride) st256_f(a + g, triad8(ld256_f(b + g), ld256_f(c + g), s));
 }
 
 // ---------------------------------------------------------------- TMA copy --
-constexpr uint32_t kTile = 32 * 1024;  // bytes per bulk copy
-constexpr int kCopyStages = 6;         // 192 KiB of shared memory in flight per SM
-constexpr size_t kCopySmem = (size_t)kCopyStages * kTile + 1024;
+// One CTA moves kCopyTiles tiles of kTile bytes: one thread arms an mbarrier per tile,
+// issues every bulk load (UBLKCP global->shared), then drains each tile shared->global as
+// it lands.  No thread touches the data.  64 KiB of shared memory per CTA, three CTAs per SM.
+constexpr uint32_t kTile = 16 * 1024;
+constexpr int kCopyTiles = 4;
+constexpr uint32_t kCopySpan = kTile * kCopyTiles;
+constexpr size_t kCopySmem = (size_t)kCopySpan + 128;
 
-__global__ void __launch_bounds__(32, 1)
-copy_tma_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint64_t ntiles) {
+__global__ void __launch_bounds__(32)
+copy_tma_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t full[kCopyStages];
+  __shared__ __align__(8) uint64_t full[kCopyTiles];
   uint8_t* tiles = reinterpret_cast<uint8_t*>(((uintptr_t)smem + 127) & ~(uintptr_t)127);
   if (threadIdx.x != 0) return;
-  for (int s = 0; s < kCopyStages; ++s) mbar_init(&full[s], 1);
+#pragma unroll
+  for (int t = 0; t < kCopyTiles; ++t) mbar_init(&full[t], 1);
   mbar_fence_init();
-
-  const uint64_t first = blockIdx.x, step = gridDim.x;
-  const uint64_t mine = first < ntiles ? (ntiles - first + step - 1) / step : 0;
-  // prologue: kCopyStages-1 loads in flight
-  uint64_t issued = 0;
-  for (; issued < mine && issued < (uint64_t)(kCopyStages - 1); ++issued) {
-    const int s = (int)(issued % kCopyStages);
-    mbar_expect_tx(&full[s], kTile);
-    bulk_g2s(tiles + (size_t)s * kTile, src + (first + issued * step) * kTile, kTile, &full[s]);
+  const uint64_t base = (uint64_t)blockIdx.x * kCopySpan;
+#pragma unroll
+  for (int t = 0; t < kCopyTiles; ++t) {
+    mbar_expect_tx(&full[t], kTile);
+    bulk_g2s(tiles + t * kTile, src + base + (uint64_t)t * kTile, kTile, &full[t]);
   }
-  for (uint64_t n = 0; n < mine; ++n) {
-    const int s = (int)(n % kCopyStages);
-    mbar_wait(&full[s], (uint32_t)((n / kCopyStages) & 1));
-    bulk_s2g(dst + (first + n * step) * kTile, tiles + (size_t)s * kTile, kTile);
-    bulk_commit();
-    if (issued < mine) {
-      // the stage to refill held tile n-1, whose store is the second-youngest group
-      bulk_wait_read<1>();
-      const int r = (int)(issued % kCopyStages);
-      mbar_expect_tx(&full[r], kTile);
-      bulk_g2s(tiles + (size_t)r * kTile, src + (first + issued * step) * kTile, kTile, &full[r]);
-      ++issued;
-    }
+#pragma unroll
+  for (int t = 0; t < kCopyTiles; ++t) {
+    mbar_wait(&full[t], 0);
+    bulk_s2g(dst + base + (uint64_t)t * kTile, tiles + t * kTile, kTile);
   }
-  bulk_wait_all<0>();
+  bulk_commit();
+  bulk_wait_read<0>();  // shared memory must stay valid until the stores have read it
 }
 
 // --------------------------------------------------------------- TMA triad --
-constexpr uint32_t kTriTile = 16 * 1024;  // bytes of each of b, c per stage; result overwrites b
-constexpr int kTriStages = 6;             // 6 * 32 KiB = 192 KiB
-constexpr int kTriConsumers = 128;
-constexpr size_t kTriSmem = (size_t)kTriStages * 2 * kTriTile + 1024;
+// One CTA per 16 KiB tile of each array: thread 0 bulk-loads the b and c tiles onto one
+// mbarrier; four warps combine them in place in shared memory (LDS.128 / STS.128), fence the
+// generic proxy against the async proxy, and thread 0 bulk-stores the result tile.
+constexpr uint32_t kTriTile = 16 * 1024;
+constexpr int kTriThreads = 128;
+constexpr size_t kTriSmem = (size_t)2 * kTriTile + 128;
 
-__global__ void __launch_bounds__(32 + kTriConsumers, 1)
+__global__ void __launch_bounds__(kTriThreads)
 triad_tma_kernel(uint8_t* __restrict__ a, const uint8_t* __restrict__ b,
-                 const uint8_t* __restrict__ c, float s, uint64_t ntiles) {
+                 const uint8_t* __restrict__ c, float s) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t full[kTriStages];
-  __shared__ __align__(8) uint64_t empty[kTriStages];
+  __shared__ __align__(8) uint64_t full;
   uint8_t* tiles = reinterpret_cast<uint8_t*>(((uintptr_t)smem + 127) & ~(uintptr_t)127);
+  const uint64_t off = (uint64_t)blockIdx.x * kTriTile;
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kTriStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(&full, 1);
     mbar_fence_init();
+    mbar_expect_tx(&full, 2 * kTriTile);
+    bulk_g2s(tiles, b + off, kTriTile, &full);
+    bulk_g2s(tiles + kTriTile, c + off, kTriTile, &full);
   }
-  __syncthreads();
-  const uint64_t first = blockIdx.x, step = gridDim.x;
-  const uint64_t mine = first < ntiles ? (ntiles - first + step - 1) / step : 0;
-
-  if (threadIdx.x < 32) {
-    if (threadIdx.x != 0) return;
-    for (uint64_t n = 0; n < mine; ++n) {  // producer
-      const int st = (int)(n % kTriStages);
-      if (n >= (uint64_t)kTriStages) mbar_wait(&empty[st], (uint32_t)(((n / kTriStages) - 1) & 1));
-      uint8_t* sb = tiles + (size_t)st * 2 * kTriTile;
-      const uint64_t off = (first + n * step) * kTriTile;
-      mbar_expect_tx(&full[st], 2 * kTriTile);
-      bulk_g2s(sb, b + off, kTriTile, &full[st]);
-      bulk_g2s(sb + kTriTile, c + off, kTriTile, &full[st]);
-    }
-    return;
-  }
-  const int ct = threadIdx.x - 32;  // consumer thread 0..127
-  for (uint64_t n = 0; n < mine; ++n) {
-    const int st = (int)(n % kTriStages);
-    mbar_wait(&full[st], (uint32_t)((n / kTriStages) & 1));
-    float4* sb = reinterpret_cast<float4*>(tiles + (size_t)st * 2 * kTriTile);
-    const float4* sc = reinterpret_cast<const float4*>(tiles + (size_t)st * 2 * kTriTile + kTriTile);
+  __syncthreads();  // barrier init visible to the waiters
+  mbar_wait(&full, 0);
+  float4* sb = reinterpret_cast<float4*>(tiles);
+  const float4* sc = reinterpret_cast<const float4*>(tiles + kTriTile);
 #pragma unroll
-    for (int k = 0; k < (int)(kTriTile / 16 / kTriConsumers); ++k) {
-      const int idx = ct + k * kTriConsumers;
-      float4 x = sb[idx];
-      const float4 y = sc[idx];
-      x.x = fmaf(s, y.x, x.x); x.y = fmaf(s, y.y, x.y);
-      x.z = fmaf(s, y.z, x.z); x.w = fmaf(s, y.w, x.w);
-      sb[idx] = x;
-    }
-    fence_proxy_async_smem();
-    asm volatile("bar.sync 1, %0;" ::"n"(kTriConsumers) : "memory");
-    if (ct == 0) {
-      bulk_s2g(a + (first + n * step) * kTriTile, sb, kTriTile);
-      bulk_commit();
-      if (n > 0) {  // tile n-1's store has finished reading its stage: hand it back
-        bulk_wait_read<1>();
-        mbar_arrive(&empty[(int)((n - 1) % kTriStages)]);
-      }
-    }
+  for (int k = 0; k < (int)(kTriTile / 16 / kTriThreads); ++k) {
+    const int idx = threadIdx.x + k * kTriThreads;
+    float4 x = sb[idx];
+    const float4 y = sc[idx];
+    x.x = fmaf(s, y.x, x.x); x.y = fmaf(s, y.y, x.y);
+    x.z = fmaf(s, y.z, x.z); x.w = fmaf(s, y.w, x.w);
+    sb[idx] = x;
   }
-  if (ct == 0) bulk_wait_all<0>();
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    bulk_s2g(a + off, tiles, kTriTile);
+    bulk_commit();
+    bulk_wait_read<0>();
+  }
 }
 
 // ------------------------------------------------------------- generators ---
@@ -216,42 +203,27 @@ cudaError_t stream_kernels_configure() {
                               (int)kTriSmem);
 }
 
-template <auto kernel>
-static int resident_blocks_per_sm() {
-  static int cached = 0;
-  if (cached == 0) {
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kVecThreads, 0) != cudaSuccess || n < 1) n = 1;
-    cached = n;
-  }
-  return cached;
-}
-
-static int vec_grid(uint64_t nvec, int sm_count, int blocks_per_sm) {
-  uint64_t want = (nvec + kVecThreads - 1) / kVecThreads;
-  const uint64_t cap = (uint64_t)sm_count * blocks_per_sm;
-  if (want > cap) want = cap;
-  if (want < 1) want = 1;
-  return (int)want;
+static unsigned int chunk_grid(uint64_t nvec, uint64_t vec_per_cta) {
+  const uint64_t g = (nvec + vec_per_cta - 1) / vec_per_cta;
+  return (unsigned int)(g < 1 ? 1 : g);
 }
 
 cudaError_t launch_copy(void* dst, const void* src, uint64_t bytes, int variant, int sm_count,
                         cudaStream_t stream) {
-  // bytes is a multiple of 32.  The TMA variant moves whole 32 KiB tiles; a ragged tail (only
+  // bytes is a multiple of 32.  The TMA variant moves whole 64 KiB spans; a ragged tail (only
   // the host-buffer parity path has one) goes through the vector kernel.
+  (void)sm_count;
   uint64_t done = 0;
   if (variant == GP_STREAM_TMA) {
-    const uint64_t ntiles = bytes / kTile;
-    if (ntiles) {
-      const int grid = (int)(ntiles < (uint64_t)sm_count ? ntiles : (uint64_t)sm_count);
-      copy_tma_kernel<<<grid, 32, kCopySmem, stream>>>(reinterpret_cast<const uint8_t*>(src),
-                                                       reinterpret_cast<uint8_t*>(dst), ntiles);
-    }
-    done = ntiles * kTile;
+    const uint64_t nspans = bytes / kCopySpan;
+    if (nspans)
+      copy_tma_kernel<<<(unsigned int)nspans, 32, kCopySmem, stream>>>(
+          reinterpret_cast<const uint8_t*>(src), reinterpret_cast<uint8_t*>(dst));
+    done = nspans * kCopySpan;
   }
   if (done < bytes) {
     const uint64_t nvec = (bytes - done) / 32;
-    copy_vec_kernel<<<vec_grid(nvec, sm_count, resident_blocks_per_sm<copy_vec_kernel>()), kVecThreads, 0, stream>>>(
+    copy_vec_kernel<<<chunk_grid(nvec, kVecThreads * kCopyVecPerThread), kVecThreads, 0, stream>>>(
         reinterpret_cast<const u64x4*>(reinterpret_cast<const uint8_t*>(src) + done),
         reinterpret_cast<u64x4*>(reinterpret_cast<uint8_t*>(dst) + done), nvec);
   }
@@ -260,21 +232,20 @@ cudaError_t launch_copy(void* dst, const void* src, uint64_t bytes, int variant,
 
 cudaError_t launch_triad(float* a, const float* b, const float* c, float s, uint64_t bytes,
                          int variant, int sm_count, cudaStream_t stream) {
+  (void)sm_count;
   uint64_t done = 0;
   uint8_t* a8 = reinterpret_cast<uint8_t*>(a);
   const uint8_t* b8 = reinterpret_cast<const uint8_t*>(b);
   const uint8_t* c8 = reinterpret_cast<const uint8_t*>(c);
   if (variant == GP_STREAM_TMA) {
     const uint64_t ntiles = bytes / kTriTile;
-    if (ntiles) {
-      const int grid = (int)(ntiles < (uint64_t)sm_count ? ntiles : (uint64_t)sm_count);
-      triad_tma_kernel<<<grid, 32 + kTriConsumers, kTriSmem, stream>>>(a8, b8, c8, s, ntiles);
-    }
+    if (ntiles)
+      triad_tma_kernel<<<(unsigned int)ntiles, kTriThreads, kTriSmem, stream>>>(a8, b8, c8, s);
     done = ntiles * kTriTile;
   }
   if (done < bytes) {
     const uint64_t nvec = (bytes - done) / 32;
-    triad_vec_kernel<<<vec_grid(nvec, sm_count, resident_blocks_per_sm<triad_vec_kernel>()), kVecThreads, 0, stream>>>(
+    triad_vec_kernel<<<chunk_grid(nvec, kVecThreads * kTriVecPerThread), kVecThreads, 0, stream>>>(
         reinterpret_cast<f32x8*>(a8 + done), reinterpret_cast<const f32x8*>(b8 + done),
         reinterpret_cast<const f32x8*>(c8 + done), s, nvec);
   }
