@@ -1,0 +1,104 @@
+"""GPU parity: bf16 GEMM probe on tcgen05/TMEM through the C ABI vs the CPU oracle's fp64
+reference of the same bf16-rounded inputs.
+
+Stated tolerance: |c - ref| <= 1e-3 * SUM_k |a_ik| |b_jk| for the
+fp32 output.  Products of two bf16 values are exact in fp32, so the only error is the fp32
+accumulation over K; in practice it is ~1e-6 of SUM|a||b| and the tests also print it."""
+import os
+
+import numpy as np
+import pytest
+
+import gpuprobe
+import oracle_lib
+
+pytestmark = pytest.mark.gpu
+DEV = "0"
+TOL = 1e-3
+
+
+@pytest.fixture(params=["2", "1"], ids=["cta_group2", "cta_group1"])
+def cta_group(request):
+    old = os.environ.get("GPUPROBE_GEMM_CTA_GROUP")
+    os.environ["GPUPROBE_GEMM_CTA_GROUP"] = request.param
+    yield request.param
+    if old is None:
+        os.environ.pop("GPUPROBE_GEMM_CTA_GROUP", None)
+    else:
+        os.environ["GPUPROBE_GEMM_CTA_GROUP"] = old
+
+
+def ref_gemm(oracle, a, b, m, n, k):
+    c = np.empty((m, n), dtype=np.float64)
+    ad = np.empty((m, n), dtype=np.float64)
+    oracle.gp_cpu_gemm_ref(a.ctypes.data, b.ctypes.data, c.ctypes.data, ad.ctypes.data, m, n, k)
+    return c, ad
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 256, 64), (256, 512, 128), (512, 256, 1024),
+                                   (768, 1024, 320), (256, 256, 8192), (2560, 2304, 192)])
+def test_gemm_matches_oracle(probe, oracle, cta_group, m, n, k):
+    a = oracle_lib.gen_bf16(oracle, 0x5EED + m, 0, m * k)
+    b = oracle_lib.gen_bf16(oracle, (0x5EED + n) ^ oracle_lib.SEED_B_XOR, 0, n * k)
+    c = np.zeros((m, n), dtype=np.float32)
+    probe.gemm_host(DEV, a, b, c, m, n, k)
+    ref, absdot = ref_gemm(oracle, a, b, m, n, k)
+    assert np.isfinite(c).all()
+    scaled = np.abs(c.astype(np.float64) - ref) / np.maximum(absdot, 1e-30)
+    print(f"gemm {m}x{n}x{k} cta_group={cta_group}: max scaled err {scaled.max():.3e}")
+    assert scaled.max() <= TOL
+
+
+def test_gemm_layout_exact(probe, cta_group):
+    """A selects one column of B per row: C[i][j] = B[j][i % K] exactly — any tile, swizzle or
+    descriptor mistake shows up as a wrong element, not as rounding."""
+    m, n, k = 512, 768, 256
+    one = np.uint16(0x3F80)  # bf16 1.0
+    a = np.zeros((m, k), dtype=np.uint16)
+    a[np.arange(m), np.arange(m) % k] = one
+    rng = np.random.default_rng(7)
+    bf = rng.integers(-64, 64, size=(n, k)).astype(np.float32)  # small integers: exact in bf16
+    b = (bf.view(np.uint32) >> 16).astype(np.uint16)
+    c = np.zeros((m, n), dtype=np.float32)
+    probe.gemm_host(DEV, a, b, c, m, n, k)
+    expect = bf[:, np.arange(m) % k].T
+    assert np.array_equal(c, expect)
+
+
+def test_gemm_probe_small_and_full(cta_group):
+    with gpuprobe.Probe(keep_arena=1) as p:
+        for mnk, it in [(1024, 3), (2048, 3), (8192, 5)]:
+            g = p.gemm_probe(DEV, mnk=mnk, iters=it, warmup=1, samples=4096)
+            print(f"gemm probe {mnk}^3 cta_group={cta_group}: {g.tflops_best:.0f} TFLOP/s best, "
+                  f"max scaled err {g.max_scaled_err:.2e}, freivalds {g.freivalds_err:.2e}")
+            assert g.samples == 4096 and g.samples_bad == 0
+            assert g.max_scaled_err <= TOL and g.freivalds_err <= TOL
+            assert g.tflops_best > 1.0
+        # same seed -> same checksum (deterministic accumulation order)
+        g2 = p.gemm_probe(DEV, mnk=2048, iters=1, warmup=0, samples=16)
+        g3 = p.gemm_probe(DEV, mnk=2048, iters=1, warmup=0, samples=16)
+        assert g2.c_checksum == g3.c_checksum
+
+
+def test_gemm_detects_corruption(probe, oracle):
+    """The host-side sampled check must actually be able to fail: a different seed for the
+    reference than for the operands is a stand-in for a corrupted tensor pipe."""
+    m = n = k = 256
+    a = oracle_lib.gen_bf16(oracle, 1, 0, m * k)
+    b = oracle_lib.gen_bf16(oracle, 2, 0, n * k)
+    c = np.zeros((m, n), dtype=np.float32)
+    probe.gemm_host(DEV, a, b, c, m, n, k)
+    a2 = a.copy()
+    a2[5 * k + 3] ^= np.uint16(0x4000)  # flip one exponent bit of A[5][3]
+    ref, absdot = ref_gemm(oracle, a2, b, m, n, k)
+    scaled = np.abs(c.astype(np.float64) - ref) / np.maximum(absdot, 1e-30)
+    assert scaled[5].max() > TOL and np.delete(scaled, 5, axis=0).max() <= TOL
+
+
+def test_gemm_invalid_shapes(probe):
+    z = np.zeros(256 * 256, dtype=np.uint16)
+    c = np.zeros((256, 256), dtype=np.float32)
+    for m, n, k in [(128, 256, 64), (256, 255, 64), (256, 256, 32), (0, 256, 64)]:
+        with pytest.raises(gpuprobe.GpuProbeError) as e:
+            probe.gemm_host(DEV, z, z, c, m, n, k)
+        assert e.value.code == gpuprobe.GP_ERR_INVALID
