@@ -263,6 +263,32 @@ int gp_hbm_step(gp_ctx* ctx, const char* uuid, uint64_t bytes, uint32_t step,
                 gp_pattern_result* out /*[3]*/);
 int gp_kernel_stats(gp_ctx* ctx, const char* uuid, gp_kernel_stat* out /*[GP_K_COUNT]*/, int reset);
 
+/* Verify without allocating anything.  No counterpart in the reference.
+ *
+ * For callers that cannot call cudaMalloc: a re-grade of a GPU whose memory is
+ * already leased to pods (an allocation there fails or eats into a tenant's
+ * share), or code that must not enter the CUDA allocator because cudaMalloc and
+ * cudaFree synchronise the device.  The caller passes the DEVICE memory to grade
+ * (d_words, nwords u64 words, nwords % 64 == 0) and a DEVICE pointer for the
+ * 48-byte result; the work is enqueued on `stream` (a cudaStream_t, NULL for the
+ * default stream) of device `device_ordinal` and the call returns without
+ * synchronising — wait on the stream before reading *d_result.  Same arithmetic
+ * and same bits as gp_pattern_verify.
+ *
+ * The kernel's scratch (accumulator slots) is a fixed 33,024-byte array inside
+ * the library's device image instead of allocated memory; every GPU that loads
+ * the library holds it until the process exits.  Limits and rules:
+ *   - at most GP_NOALLOC_MAX_WORDS words per call, else GP_ERR_TOO_LARGE;
+ *   - the first call on each device looks the array's address up
+ *     (cudaGetSymbolAddress); make that first call outside any stream capture;
+ *   - all calls on a device share the one array: two calls whose kernels overlap
+ *     on the GPU (different streams, or different threads) race and return
+ *     garbage — serialise them; calls on one stream are safe;
+ *   - calls cudaSetDevice(device_ordinal) on the calling thread. */
+#define GP_NOALLOC_MAX_WORDS (1ull << 35) /* 256 GiB of graded memory per call */
+int gp_pattern_verify_noalloc(int device_ordinal, const uint64_t* d_words, uint64_t nwords, int kind,
+                              int pass, gp_pattern_result* d_result, void* stream);
+
 /* Test-only fault injection: flip `bit` of arena word `word_index`. */
 int gp_inject_bitflip(gp_ctx* ctx, const char* uuid, uint64_t word_index, int bit);
 

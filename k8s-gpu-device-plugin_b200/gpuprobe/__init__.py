@@ -126,6 +126,7 @@ ABI = [
     ("gp_hbm_step", C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.c_uint32, _P(PatternResult)]),
     ("gp_kernel_stats", C.c_int, [C.c_void_p, C.c_char_p, _P(KernelStat), C.c_int]),
     ("gp_inject_bitflip", C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.c_int]),
+    ("gp_pattern_verify_noalloc", C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     ("gp_probe_p2p", C.c_int, [C.c_void_p, C.c_int, C.c_size_t, C.c_int, _P(C.c_double)]),
     ("gp_probe_allreduce", C.c_int, [C.c_void_p, C.c_int, C.c_size_t, C.c_uint32, C.c_uint32, _P(C.c_double), _P(C.c_double)]),
 ]
@@ -150,6 +151,22 @@ def load(path: Optional[str] = None) -> C.CDLL:
     if path is None:
         _lib = lib
     return lib
+
+
+GP_NOALLOC_MAX_WORDS = 1 << 35
+
+
+def pattern_verify_noalloc(ordinal: int, d_words_ptr: int, nwords: int, kind: int, pas: int,
+                           d_result_ptr: int, stream: int = 0) -> None:
+    """gp_pattern_verify_noalloc: caller-owned device memory in, 48-byte device result out,
+    enqueued on `stream` without synchronising and without allocating.  Needs no gp_ctx.
+    Raises GpuProbeError on a non-zero return code."""
+    lib = load()
+    rc = lib.gp_pattern_verify_noalloc(ordinal, C.c_void_p(d_words_ptr), nwords, kind, pas,
+                                       C.c_void_p(d_result_ptr), C.c_void_p(stream))
+    if rc != GP_OK:
+        raise GpuProbeError(rc, "gp_pattern_verify_noalloc",
+                            (lib.gp_last_error_detail() or b"").decode(errors="replace"))
 
 
 def _u(uuid) -> bytes:
