@@ -491,6 +491,7 @@ int gp_init(const gp_config* cfg, gp_ctx** out) {
 
 void gp_shutdown(gp_ctx* ctx) {
   if (!ctx) return;
+  nccl_teardown(ctx);
   for (auto& d : ctx->devs) {
     std::lock_guard<std::mutex> g(d->mu);
     if (!d->ready && !d->arena) continue;

@@ -73,6 +73,7 @@ int gemm_host_locked(Ctx* ctx, Device* d, const uint16_t* a, const uint16_t* b, 
 int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps);
 int allreduce_probe(Ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters,
                     double* algbw, double* busbw);
+void nccl_teardown(Ctx* ctx);
 
 }  // namespace gp
 

@@ -1,6 +1,372 @@
-// placeholder until the peer kernels land
+// p2p.cu — the only cross-device probes (K4a / K4b of SURVEY.md §8).
+//
+//   gp_probe_p2p       : NVLink bandwidth matrix with IN-KERNEL peer loads / stores — the
+//                        kernel runs on GPU `src` and dereferences a pointer into GPU `dst`'s
+//                        memory (LDG / STG on a peer-mapped address), no copy engine.
+//   gp_probe_allreduce : ncclAllReduce(sum, fp32, in place) bus bandwidth, single process,
+//                        one communicator per device (ncclCommInitAll), group launch.
+//
+// No reference counterpart: the reference's only topology input is go-gpuallocator's NVML
+// link query (plugin/plugin.go:259-276); it moves no bytes.  Algorithmic bytes:
+// P2P S bytes per direction per transfer; all-reduce algbw S/t, busbw S/t * 2(n-1)/n.
+//
+// Pairs are scheduled as the n-1 rounds of a 1-factorisation (circle method): in a round every
+// GPU is in exactly one pair, so all GPUs are busy and no GPU serves two peers at once.  A
+// unidirectional round runs in two phases (a->b for every pair, then b->a); the bidirectional
+// mode runs both directions of every pair at once and reports each direction.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <vector>
+
+#include "common.cuh"
 #include "engine.h"
+
 namespace gp {
-int p2p_probe(Ctx*, int, size_t, int, double*) { set_error("p2p probe not built"); return GP_ERR_UNSUPPORTED; }
-int allreduce_probe(Ctx*, int, size_t, uint32_t, uint32_t, double*, double*) { set_error("allreduce probe not built"); return GP_ERR_UNSUPPORTED; }
+
+#define CU_OR_RETURN(call)                                               \
+  do {                                                                   \
+    cudaError_t e__ = (call);                                            \
+    if (e__ != cudaSuccess) return ::gp::cuda_fail(e__, #call, nullptr); \
+  } while (0)
+
+constexpr int kP2PThreads = 512;
+constexpr int kP2PUnroll = 4;  // 4 x 32 B in flight per thread: peer latency is ~2-4k cycles
+
+// kernel on `src`: read every vector of the peer buffer, fold into a value nobody stores
+__global__ void __launch_bounds__(kP2PThreads)
+p2p_read_kernel(const u64x4* __restrict__ peer, uint64_t nvec, unsigned long long* __restrict__ sink) {
+  const uint64_t stride = (uint64_t)gridDim.x * kP2PThreads;
+  uint64_t g = (uint64_t)blockIdx.x * kP2PThreads + threadIdx.x;
+  uint64_t acc = 0;
+  for (; g + (kP2PUnroll - 1) * stride < nvec; g += kP2PUnroll * stride) {
+    u64x4 v[kP2PUnroll];
+#pragma unroll
+    for (int u = 0; u < kP2PUnroll; ++u) v[u] = ld256_stream(peer + g + u * stride);
+#pragma unroll
+    for (int u = 0; u < kP2PUnroll; ++u) acc += (v[u].v[0] ^ v[u].v[1]) + (v[u].v[2] ^ v[u].v[3]);
+  }
+  for (; g < nvec; g += stride) {
+    const u64x4 v = ld256_stream(peer + g);
+    acc += (v.v[0] ^ v.v[1]) + (v.v[2] ^ v.v[3]);
+  }
+  if (acc == 0x9E3779B97F4A7C15ull) atomicAdd(sink, 1ull);  // keeps the loads alive
 }
+
+// kernel on `src`: store the address pattern into the peer buffer
+__global__ void __launch_bounds__(kP2PThreads)
+p2p_write_kernel(u64x4* __restrict__ peer, uint64_t nvec, uint64_t tag) {
+  const uint64_t stride = (uint64_t)gridDim.x * kP2PThreads;
+  for (uint64_t g = (uint64_t)blockIdx.x * kP2PThreads + threadIdx.x; g < nvec; g += stride) {
+    u64x4 v;
+    v.v[0] = tag; v.v[1] = g; v.v[2] = ~g; v.v[3] = tag ^ g;
+    st256_stream(peer + g, v);
+  }
+}
+
+__global__ void p2p_check_kernel(const u64x4* __restrict__ buf, uint64_t nvec, uint64_t tag,
+                                 unsigned long long* __restrict__ bad) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  unsigned long long b = 0;
+  for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < nvec; g += stride) {
+    const u64x4 v = buf[g];
+    b += (v.v[0] != tag) | (v.v[1] != g) | (v.v[2] != ~g) | (v.v[3] != (tag ^ g));
+  }
+  if (b) atomicAdd(bad, b);
+}
+
+static int p2p_grid(uint64_t nvec, int sm_count) {
+  const uint64_t want = (nvec + kP2PThreads - 1) / kP2PThreads;
+  const uint64_t cap = (uint64_t)sm_count * 4;  // 2048 threads per SM
+  return (int)std::max<uint64_t>(1, std::min(want, cap));
+}
+
+// 1-factorisation of K_n (n even) by the circle method; odd n gets a bye.
+static std::vector<std::vector<std::pair<int, int>>> rounds_for(int n) {
+  std::vector<std::vector<std::pair<int, int>>> out;
+  const int m = (n % 2) ? n + 1 : n;
+  for (int r = 0; r < m - 1; ++r) {
+    std::vector<std::pair<int, int>> round;
+    for (int i = 0; i < m / 2; ++i) {
+      int a = (r + i) % (m - 1);
+      int b = (i == 0) ? m - 1 : (r + m - 1 - i) % (m - 1);
+      if (a >= n || b >= n) continue;
+      if (a > b) std::swap(a, b);
+      round.push_back({a, b});
+    }
+    out.push_back(round);
+  }
+  return out;
+}
+
+struct Xfer {
+  int src, dst;
+};
+
+// run a set of transfers concurrently (one per src device), return best-of-iters GB/s of each
+static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, bool write, int iters,
+                     std::vector<double>* gbps_out) {
+  const uint64_t nvec = bytes / 32;
+  gbps_out->assign(xs.size(), 0.0);
+  std::vector<float> best(xs.size(), 1e30f);
+  for (int it = 0; it < iters + 1; ++it) {  // first pass is the warm-up
+    for (size_t i = 0; i < xs.size(); ++i) {
+      Device* s = ctx->devs[(size_t)xs[i].src].get();
+      Device* d = ctx->devs[(size_t)xs[i].dst].get();
+      CU_OR_RETURN(cudaSetDevice(s->ordinal));
+      CU_OR_RETURN(cudaEventRecord(s->events[0], s->stream));
+      if (write)
+        p2p_write_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(
+            reinterpret_cast<u64x4*>(d->arena), nvec, 0xC0DE0000ull + (uint64_t)xs[i].src);
+      else
+        p2p_read_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(
+            reinterpret_cast<const u64x4*>(d->arena), nvec, s->d_count);
+      CU_OR_RETURN(cudaGetLastError());
+      CU_OR_RETURN(cudaEventRecord(s->events[1], s->stream));
+    }
+    for (size_t i = 0; i < xs.size(); ++i) {
+      Device* s = ctx->devs[(size_t)xs[i].src].get();
+      CU_OR_RETURN(cudaSetDevice(s->ordinal));
+      CU_OR_RETURN(cudaStreamSynchronize(s->stream));
+      float ms = 0;
+      CU_OR_RETURN(cudaEventElapsedTime(&ms, s->events[0], s->events[1]));
+      if (it > 0) {
+        best[i] = std::min(best[i], ms);
+        s->stats[GP_K_P2P].launches += 1;
+        s->stats[GP_K_P2P].total_ms += ms;
+        s->stats[GP_K_P2P].algo_bytes += (double)bytes;
+      }
+    }
+  }
+  for (size_t i = 0; i < xs.size(); ++i) (*gbps_out)[i] = (double)bytes / (best[i] * 1e-3) / 1e9;
+  return GP_OK;
+}
+
+int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
+  if (ngpus > (int)ctx->devs.size()) { set_error("ngpus %d > visible %zu", ngpus, ctx->devs.size()); return GP_ERR_NO_DEVICE; }
+  if (bytes == 0 || bytes % 32) { set_error("bytes must be a non-zero multiple of 32"); return GP_ERR_INVALID; }
+  std::lock_guard<std::mutex> multi(ctx->multi_mu);
+  std::vector<std::unique_lock<std::mutex>> locks;
+  for (int i = 0; i < ngpus; ++i) locks.emplace_back(ctx->devs[(size_t)i]->mu);  // ordinal order: no deadlock
+  for (int i = 0; i < ngpus * ngpus; ++i) gbps[i] = 0.0;
+  for (int i = 0; i < ngpus; ++i) {
+    Device* d = ctx->devs[(size_t)i].get();
+    int rc = device_prepare(ctx, d);
+    if (rc) return rc;
+    rc = ensure_arena(ctx, d, std::max<size_t>(bytes, 1 << 20));
+    if (rc) return rc;
+    d->triad_operands_bytes = 0;
+    CU_OR_RETURN(cudaMemsetAsync(d->arena, 0x5A, bytes, d->stream));
+    CU_OR_RETURN(cudaMemsetAsync(d->d_count, 0, sizeof(unsigned long long), d->stream));
+    CU_OR_RETURN(cudaStreamSynchronize(d->stream));
+  }
+  for (int i = 0; i < ngpus; ++i) {
+    CU_OR_RETURN(cudaSetDevice(i));
+    for (int j = 0; j < ngpus; ++j) {
+      if (i == j) continue;
+      int can = 0;
+      CU_OR_RETURN(cudaDeviceCanAccessPeer(&can, i, j));
+      if (!can) { set_error("device %d cannot access peer %d", i, j); return GP_ERR_UNSUPPORTED; }
+      cudaError_t e = cudaDeviceEnablePeerAccess(j, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, "cudaDeviceEnablePeerAccess", nullptr);
+      (void)cudaGetLastError();
+    }
+  }
+  const bool write = dir != 0;
+  const int iters = 3;
+  std::vector<double> r;
+  // diagonal: the same kernel on local memory, all GPUs at once
+  {
+    std::vector<Xfer> xs;
+    for (int i = 0; i < ngpus; ++i) xs.push_back({i, i});
+    int rc = run_xfers(ctx, xs, bytes, write, iters, &r);
+    if (rc) return rc;
+    for (int i = 0; i < ngpus; ++i) gbps[i * ngpus + i] = r[(size_t)i];
+  }
+  for (const auto& round : rounds_for(ngpus)) {
+    if (dir == 2) {
+      std::vector<Xfer> xs;
+      for (auto pr : round) { xs.push_back({pr.first, pr.second}); xs.push_back({pr.second, pr.first}); }
+      int rc = run_xfers(ctx, xs, bytes, true, iters, &r);
+      if (rc) return rc;
+      for (size_t i = 0; i < xs.size(); ++i) gbps[xs[i].src * ngpus + xs[i].dst] = r[i];
+    } else {
+      for (int phase = 0; phase < 2; ++phase) {
+        std::vector<Xfer> xs;
+        for (auto pr : round) xs.push_back(phase == 0 ? Xfer{pr.first, pr.second} : Xfer{pr.second, pr.first});
+        int rc = run_xfers(ctx, xs, bytes, write, iters, &r);
+        if (rc) return rc;
+        for (size_t i = 0; i < xs.size(); ++i) gbps[xs[i].src * ngpus + xs[i].dst] = r[i];
+      }
+    }
+  }
+  // a write probe must actually have landed: check what the last writer left in each arena
+  if (write && ngpus > 1) {
+    const auto rounds = rounds_for(ngpus);
+    std::vector<int> last_writer((size_t)ngpus, -1);
+    for (const auto& round : rounds)
+      for (auto pr : round) { last_writer[(size_t)pr.second] = pr.first; last_writer[(size_t)pr.first] = pr.second; }
+    // within a round, phase order (uni) is a->b then b->a; in both modes each arena's last writer is its partner
+    for (int i = 0; i < ngpus; ++i) {
+      Device* d = ctx->devs[(size_t)i].get();
+      CU_OR_RETURN(cudaSetDevice(i));
+      CU_OR_RETURN(cudaMemsetAsync(d->d_count, 0, sizeof(unsigned long long), d->stream));
+      p2p_check_kernel<<<d->sm_count * 4, 256, 0, d->stream>>>(reinterpret_cast<const u64x4*>(d->arena), bytes / 32,
+                                                              0xC0DE0000ull + (uint64_t)last_writer[(size_t)i], d->d_count);
+      CU_OR_RETURN(cudaGetLastError());
+      CU_OR_RETURN(cudaMemcpyAsync(d->h_count, d->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, d->stream));
+      CU_OR_RETURN(cudaStreamSynchronize(d->stream));
+      if (*d->h_count) { set_error("peer writes into device %d did not land intact (%llu bad vectors)", i, *d->h_count); return GP_ERR_CUDA; }
+    }
+  }
+  if (!ctx->cfg.keep_arena)
+    for (int i = 0; i < ngpus; ++i) free_arena(ctx->devs[(size_t)i].get());
+  return GP_OK;
+}
+
+// ------------------------------------------------------------------ NCCL ----
+struct NcclApi {
+  void* handle = nullptr;
+  decltype(&ncclCommInitAll) CommInitAll = nullptr;
+  decltype(&ncclCommDestroy) CommDestroy = nullptr;
+  decltype(&ncclAllReduce) AllReduce = nullptr;
+  decltype(&ncclGroupStart) GroupStart = nullptr;
+  decltype(&ncclGroupEnd) GroupEnd = nullptr;
+  decltype(&ncclGetErrorString) GetErrorString = nullptr;
+  std::map<int, std::vector<ncclComm_t>> comms;  // by rank count
+};
+
+static NcclApi* nccl_api(Ctx* ctx) {
+  if (ctx->nccl_handle) return reinterpret_cast<NcclApi*>(ctx->nccl_handle);
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+  if (!h) { set_error("libnccl.so.2 not loadable: %s", dlerror()); return nullptr; }
+  NcclApi* a = new NcclApi();
+  a->handle = h;
+  a->CommInitAll = reinterpret_cast<decltype(a->CommInitAll)>(dlsym(h, "ncclCommInitAll"));
+  a->CommDestroy = reinterpret_cast<decltype(a->CommDestroy)>(dlsym(h, "ncclCommDestroy"));
+  a->AllReduce = reinterpret_cast<decltype(a->AllReduce)>(dlsym(h, "ncclAllReduce"));
+  a->GroupStart = reinterpret_cast<decltype(a->GroupStart)>(dlsym(h, "ncclGroupStart"));
+  a->GroupEnd = reinterpret_cast<decltype(a->GroupEnd)>(dlsym(h, "ncclGroupEnd"));
+  a->GetErrorString = reinterpret_cast<decltype(a->GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+  if (!a->CommInitAll || !a->CommDestroy || !a->AllReduce || !a->GroupStart || !a->GroupEnd) {
+    set_error("libnccl is missing a required symbol");
+    delete a;
+    return nullptr;
+  }
+  ctx->nccl_handle = a;
+  return a;
+}
+
+void nccl_teardown(Ctx* ctx) {
+  if (!ctx->nccl_handle) return;
+  NcclApi* a = reinterpret_cast<NcclApi*>(ctx->nccl_handle);
+  for (auto& kv : a->comms)
+    for (ncclComm_t c : kv.second) a->CommDestroy(c);
+  delete a;  // the library stays mapped: unloading NCCL under live CUDA contexts is not worth the risk
+  ctx->nccl_handle = nullptr;
+}
+
+#define NCCL_OR_RETURN(call)                                                                  \
+  do {                                                                                        \
+    ncclResult_t r__ = (call);                                                                \
+    if (r__ != ncclSuccess) {                                                                 \
+      set_error("%s: %s (%d)", #call, api->GetErrorString ? api->GetErrorString(r__) : "?", (int)r__); \
+      return GP_ERR_NCCL;                                                                     \
+    }                                                                                         \
+  } while (0)
+
+__global__ void fill_f32_kernel(float* p, uint64_t n, float v) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
+}
+
+int allreduce_probe(Ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters, double* algbw,
+                    double* busbw) {
+  if (nranks > (int)ctx->devs.size()) { set_error("nranks %d > visible %zu", nranks, ctx->devs.size()); return GP_ERR_NO_DEVICE; }
+  if (bytes == 0 || bytes % 4) { set_error("bytes must be a non-zero multiple of 4"); return GP_ERR_INVALID; }
+  std::lock_guard<std::mutex> multi(ctx->multi_mu);
+  NcclApi* api = nccl_api(ctx);
+  if (!api) return GP_ERR_NCCL;
+  std::vector<std::unique_lock<std::mutex>> locks;
+  for (int i = 0; i < nranks; ++i) locks.emplace_back(ctx->devs[(size_t)i]->mu);
+  const uint64_t count = bytes / 4;
+  for (int i = 0; i < nranks; ++i) {
+    Device* d = ctx->devs[(size_t)i].get();
+    int rc = device_prepare(ctx, d);
+    if (rc) return rc;
+    rc = ensure_arena(ctx, d, std::max<size_t>(bytes, 1 << 20));
+    if (rc) return rc;
+    d->triad_operands_bytes = 0;
+    fill_f32_kernel<<<d->sm_count * 4, 256, 0, d->stream>>>(reinterpret_cast<float*>(d->arena), count, (float)(i + 1));
+    CU_OR_RETURN(cudaGetLastError());
+    CU_OR_RETURN(cudaStreamSynchronize(d->stream));
+  }
+  auto it = api->comms.find(nranks);
+  if (it == api->comms.end()) {
+    std::vector<ncclComm_t> comms((size_t)nranks);
+    std::vector<int> devlist((size_t)nranks);
+    for (int i = 0; i < nranks; ++i) devlist[(size_t)i] = i;
+    NCCL_OR_RETURN(api->CommInitAll(comms.data(), nranks, devlist.data()));
+    it = api->comms.emplace(nranks, comms).first;
+  }
+  std::vector<ncclComm_t>& comms = it->second;
+  auto one = [&]() -> int {
+    NCCL_OR_RETURN(api->GroupStart());
+    for (int i = 0; i < nranks; ++i) {
+      Device* d = ctx->devs[(size_t)i].get();
+      NCCL_OR_RETURN(api->AllReduce(d->arena, d->arena, count, ncclFloat, ncclSum, comms[(size_t)i], d->stream));
+    }
+    NCCL_OR_RETURN(api->GroupEnd());
+    return GP_OK;
+  };
+  // correctness: after ONE all-reduce every element is n(n+1)/2 on every rank
+  int rc = one();
+  if (rc) return rc;
+  const float expect = (float)(nranks * (nranks + 1) / 2);
+  for (int i = 0; i < nranks; ++i) {
+    Device* d = ctx->devs[(size_t)i].get();
+    CU_OR_RETURN(cudaSetDevice(i));
+    CU_OR_RETURN(cudaStreamSynchronize(d->stream));
+    float probe3[3];
+    const uint64_t idx[3] = {0, count / 2, count - 1};
+    for (int q = 0; q < 3; ++q)
+      CU_OR_RETURN(cudaMemcpy(&probe3[q], reinterpret_cast<float*>(d->arena) + idx[q], 4, cudaMemcpyDeviceToHost));
+    for (int q = 0; q < 3; ++q)
+      if (probe3[q] != expect) { set_error("all-reduce result %g != %g on rank %d", probe3[q], expect, i); return GP_ERR_NCCL; }
+  }
+  for (uint32_t w = 0; w < warmup; ++w) { rc = one(); if (rc) return rc; }
+  for (int i = 0; i < nranks; ++i) {
+    Device* d = ctx->devs[(size_t)i].get();
+    CU_OR_RETURN(cudaSetDevice(i));
+    CU_OR_RETURN(cudaStreamSynchronize(d->stream));
+  }
+  for (int i = 0; i < nranks; ++i) {
+    Device* d = ctx->devs[(size_t)i].get();
+    CU_OR_RETURN(cudaSetDevice(i));
+    CU_OR_RETURN(cudaEventRecord(d->events[0], d->stream));
+  }
+  for (uint32_t k = 0; k < iters; ++k) { rc = one(); if (rc) return rc; }
+  double worst_ms = 0;
+  for (int i = 0; i < nranks; ++i) {
+    Device* d = ctx->devs[(size_t)i].get();
+    CU_OR_RETURN(cudaSetDevice(i));
+    CU_OR_RETURN(cudaEventRecord(d->events[1], d->stream));
+    CU_OR_RETURN(cudaStreamSynchronize(d->stream));
+    float ms = 0;
+    CU_OR_RETURN(cudaEventElapsedTime(&ms, d->events[0], d->events[1]));
+    worst_ms = std::max(worst_ms, (double)ms);  // max over ranks, on the device
+  }
+  const double t = worst_ms * 1e-3 / iters;
+  const double alg = (double)bytes / t / 1e9;
+  if (algbw) *algbw = alg;
+  if (busbw) *busbw = alg * 2.0 * (nranks - 1) / nranks;
+  if (!ctx->cfg.keep_arena)
+    for (int i = 0; i < nranks; ++i) free_arena(ctx->devs[(size_t)i].get());
+  return GP_OK;
+}
+
+}  // namespace gp
