@@ -9,7 +9,23 @@ SRCS := $(CSRC)/engine.cu $(CSRC)/pattern.cu $(CSRC)/stream.cu $(CSRC)/gemm.cu $
 OBJS := $(SRCS:.cu=.o)
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/gpuprobe.h
 
-all: $(LIB) oracle
+HOST := $(PKG)/host
+HOST_HDRS := $(wildcard $(HOST)/*.hpp) include/gpuprobe.h
+CXX ?= g++
+CXXFLAGS := -O2 -std=c++17 -Wall -Wextra -pthread
+
+all: $(LIB) oracle host
+
+host: $(HOST)/host_selftest $(HOST)/gpuprobe-slice $(HOST)/plugin_sim
+
+$(HOST)/host_selftest: $(HOST)/host_selftest.cpp $(HOST_HDRS)
+	$(CXX) $(CXXFLAGS) -o $@ $<
+
+$(HOST)/gpuprobe-slice: $(HOST)/probe_slice.cpp $(LIB) include/gpuprobe.h
+	$(CXX) $(CXXFLAGS) -o $@ $< -L$(PKG) -lgpuprobe -Wl,-rpath,'$$ORIGIN/..'
+
+$(HOST)/plugin_sim: $(HOST)/plugin_sim.cpp $(LIB) $(HOST_HDRS)
+	$(CXX) $(CXXFLAGS) -o $@ $< -L$(PKG) -lgpuprobe -Wl,-rpath,'$$ORIGIN/..'
 
 $(CSRC)/%.o: $(CSRC)/%.cu $(HDRS)
 	$(NVCC) $(NVFLAGS) -c -o $@ $< 2> $@.ptxas.log || (cat $@.ptxas.log; exit 1)
@@ -21,7 +37,7 @@ oracle:
 	$(MAKE) -C oracle
 
 clean:
-	rm -f $(OBJS) $(CSRC)/*.ptxas.log $(LIB)
+	rm -f $(OBJS) $(CSRC)/*.ptxas.log $(LIB) $(HOST)/host_selftest $(HOST)/gpuprobe-slice $(HOST)/plugin_sim
 	$(MAKE) -C oracle clean
 
-.PHONY: all oracle clean
+.PHONY: all oracle host clean

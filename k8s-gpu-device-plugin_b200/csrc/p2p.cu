@@ -18,6 +18,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <vector>
@@ -64,6 +65,37 @@ p2p_write_kernel(u64x4* __restrict__ peer, uint64_t nvec, uint64_t tag) {
     u64x4 v;
     v.v[0] = tag; v.v[1] = g; v.v[2] = ~g; v.v[3] = tag ^ g;
     st256_stream(peer + g, v);
+  }
+}
+
+// non-persistent shapes: one CTA per contiguous chunk (kP2PThreads x U vectors), no loop
+template <int U>
+__global__ void __launch_bounds__(kP2PThreads)
+p2p_read_np_kernel(const u64x4* __restrict__ peer, uint64_t nvec, unsigned long long* __restrict__ sink) {
+  const uint64_t g0 = (uint64_t)blockIdx.x * (kP2PThreads * U) + threadIdx.x;
+  uint64_t acc = 0;
+  u64x4 v[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const uint64_t g = g0 + (uint64_t)u * kP2PThreads;
+    if (g < nvec) v[u] = ld256_stream(peer + g); else v[u] = u64x4{{0, 0, 0, 0}};
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) acc += (v[u].v[0] ^ v[u].v[1]) + (v[u].v[2] ^ v[u].v[3]);
+  if (acc == 0x9E3779B97F4A7C15ull) atomicAdd(sink, 1ull);
+}
+template <int U>
+__global__ void __launch_bounds__(kP2PThreads)
+p2p_write_np_kernel(u64x4* __restrict__ peer, uint64_t nvec, uint64_t tag) {
+  const uint64_t g0 = (uint64_t)blockIdx.x * (kP2PThreads * U) + threadIdx.x;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const uint64_t g = g0 + (uint64_t)u * kP2PThreads;
+    if (g < nvec) {
+      u64x4 v;
+      v.v[0] = tag; v.v[1] = g; v.v[2] = ~g; v.v[3] = tag ^ g;
+      st256_stream(peer + g, v);
+    }
   }
 }
 
@@ -118,12 +150,26 @@ static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, bool w
       Device* d = ctx->devs[(size_t)xs[i].dst].get();
       CU_OR_RETURN(cudaSetDevice(s->ordinal));
       CU_OR_RETURN(cudaEventRecord(s->events[0], s->stream));
-      if (write)
-        p2p_write_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(
-            reinterpret_cast<u64x4*>(d->arena), nvec, 0xC0DE0000ull + (uint64_t)xs[i].src);
-      else
-        p2p_read_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(
-            reinterpret_cast<const u64x4*>(d->arena), nvec, s->d_count);
+      const uint64_t tag = 0xC0DE0000ull + (uint64_t)xs[i].src;
+      u64x4* pa = reinterpret_cast<u64x4*>(d->arena);
+      // Measured on 2 x B200 (tools/p2p_shapes.py): read 776-785 GB/s and write 713 GB/s per direction at
+      // 1 GiB for EVERY launch shape tried — the link protocol, not the kernel, is the limit — so the
+      // default is the non-persistent shape the local kernels use; the others stay for experiments.
+      static const int shape = getenv("GPUPROBE_P2P_SHAPE") ? atoi(getenv("GPUPROBE_P2P_SHAPE")) : 1;
+      auto npgrid = [&](int U) { return (unsigned)((nvec + (uint64_t)kP2PThreads * U - 1) / ((uint64_t)kP2PThreads * U)); };
+      if (write) {
+        if (shape == 1) p2p_write_np_kernel<1><<<npgrid(1), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
+        else if (shape == 2) p2p_write_np_kernel<4><<<npgrid(4), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
+        else if (shape == 3) p2p_write_kernel<<<s->sm_count * 2, kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
+        else if (shape == 4) p2p_write_kernel<<<s->sm_count, kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
+        else p2p_write_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
+      } else {
+        if (shape == 1) p2p_read_np_kernel<2><<<npgrid(2), kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
+        else if (shape == 2) p2p_read_np_kernel<8><<<npgrid(8), kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
+        else if (shape == 3) p2p_read_kernel<<<s->sm_count * 2, kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
+        else if (shape == 4) p2p_read_kernel<<<s->sm_count, kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
+        else p2p_read_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
+      }
       CU_OR_RETURN(cudaGetLastError());
       CU_OR_RETURN(cudaEventRecord(s->events[1], s->stream));
     }
@@ -241,7 +287,13 @@ struct NcclApi {
 
 static NcclApi* nccl_api(Ctx* ctx) {
   if (ctx->nccl_handle) return reinterpret_cast<NcclApi*>(ctx->nccl_handle);
-  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+  // Use the NCCL the process already has, if any (a host that links or has loaded NCCL must not
+  // end up with a second copy under the same soname); otherwise the system one, or the path in
+  // GPUPROBE_NCCL_LIB.
+  void* h = nullptr;
+  if (const char* path = getenv("GPUPROBE_NCCL_LIB")) h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
   if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
   if (!h) { set_error("libnccl.so.2 not loadable: %s", dlerror()); return nullptr; }
   NcclApi* a = new NcclApi();

@@ -1,0 +1,116 @@
+// plugin_sim — walks the reference's start-up path (main.go:74-131 -> plugin/manager.go:56-99)
+// with the probe wired in, on real GPUs, and prints one JSON document:
+//   NewDeviceMap -> GradeDevices -> ListAndWatch first list -> GET /probe -> GET /metrics
+// There is no kubelet, gRPC or HTTP server here (out of scope); the handlers are called
+// directly.  Used by tests/test_host_gpu.py.
+//   plugin_sim [--hbm-mib N] [--pattern-mib N] [--wo N] [--gemm N] [--mask M] [--slice BIN] [--min-copy G]
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+
+#include "router.hpp"
+
+using namespace plugin;
+
+// deviceInfo backed by the probe library's enumeration (the reference's nvmlDevice,
+// device/device.go:21-181, asks NVML; CUDA reports the same UUIDs)
+struct CudaDeviceInfo : deviceInfo {
+  gp_device_result id;
+  std::pair<std::string, Error> GetUUID() override { return {id.uuid, std::nullopt}; }
+  std::pair<std::vector<std::string>, Error> GetPaths() override {
+    return {{"/dev/nvidia" + std::to_string(id.ordinal)}, std::nullopt};
+  }
+  std::tuple<bool, int, Error> GetNumaNode() override { return {false, 0, std::nullopt}; }
+  std::pair<uint64_t, Error> GetTotalMemory() override { return {id.total_mem, std::nullopt}; }
+  std::pair<std::string, Error> GetComputeCapability() override {
+    return {std::to_string(id.cc_major) + "." + std::to_string(id.cc_minor), std::nullopt};
+  }
+};
+
+static std::string listJson(const std::vector<PluginDevice>& l) {
+  std::string s = "[";
+  for (size_t i = 0; i < l.size(); ++i)
+    s += std::string(i ? "," : "") + "{\"ID\":\"" + l[i].ID + "\",\"health\":\"" + l[i].Health + "\"}";
+  return s + "]";
+}
+
+int main(int argc, char** argv) {
+  gp_config cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.struct_size = sizeof(cfg);
+  cfg.abi_version = GP_ABI_VERSION;
+  cfg.hbm_bytes = 256ull << 20;
+  cfg.pattern_bytes = 64ull << 20;
+  cfg.wo_passes = 4;
+  cfg.gemm_mnk = 1024;
+  cfg.iters = 3;
+  cfg.warmup = 1;
+  uint32_t mask = GP_PROBE_ALL_SINGLE;
+  std::string slice_bin;
+  for (int i = 1; i + 1 < argc; i += 2) {
+    const std::string a = argv[i];
+    const char* v = argv[i + 1];
+    if (a == "--hbm-mib") cfg.hbm_bytes = strtoull(v, nullptr, 10) << 20;
+    else if (a == "--pattern-mib") cfg.pattern_bytes = strtoull(v, nullptr, 10) << 20;
+    else if (a == "--wo") cfg.wo_passes = (uint32_t)atoi(v);
+    else if (a == "--gemm") cfg.gemm_mnk = (uint32_t)atoi(v);
+    else if (a == "--mask") mask = (uint32_t)atoi(v);
+    else if (a == "--slice") slice_bin = v;
+    else if (a == "--min-copy") cfg.min_copy_gbps = atof(v);
+  }
+  GpuProbeBackend be(&cfg, slice_bin);
+  if (be.init_rc()) {
+    printf("{\"error\":\"gp_init: %s\"}\n", be.init_error().c_str());
+    return 1;
+  }
+  // NewDeviceMap (device_map.go:24-75): one entry per visible GPU under nvidia.com/gpu
+  DeviceMap dm;
+  const int n = gp_device_count(be.ctx());
+  for (int i = 0; i < n; ++i) {
+    CudaDeviceInfo info;
+    char uuid[64];
+    gp_device_uuid(be.ctx(), i, uuid, sizeof(uuid));
+    gp_probe_device(be.ctx(), uuid, 0, &info.id);  // mask 0: identity only
+    if (!matchResourcePattern("*", "NVIDIA B200")) return 2;
+    if (auto e = dm.setEntry("nvidia.com/gpu", std::to_string(i), info)) { printf("{\"error\":\"%s\"}\n", e->c_str()); return 1; }
+    if (!slice_bin.empty() && i == 0) {
+      // no MIG on this box: exercise the child-process path by naming GPU 0 as slice "0:0" of a
+      // second resource; CUDA_VISIBLE_DEVICES accepts a GPU uuid exactly as it accepts a MIG uuid
+      struct SliceInfo : CudaDeviceInfo {
+        std::pair<std::string, Error> GetUUID() override { return {std::string(id.uuid) + "::1", std::nullopt}; }
+      } si;
+      si.id = info.id;
+      if (auto e = dm.setEntry("nvidia.com/mig-sim", "0:0", si)) { printf("{\"error\":\"%s\"}\n", e->c_str()); return 1; }
+    }
+  }
+  std::vector<std::string> log;
+  const int unhealthy = GradeDevices(dm, be, mask, &log);
+  ProbeMetrics metrics;
+  for (auto& d : dm.All()) metrics.Update(*d);
+
+  NvidiaDevicePlugin plug("nvidia.com/gpu", dm.m["nvidia.com/gpu"]);
+  std::vector<std::string> lists;
+  std::thread law([&] {
+    plug.ListAndWatch([&](const std::vector<PluginDevice>& l) { lists.push_back(listJson(l)); return true; });
+  });
+  API api(&dm, &be, &metrics, mask, [&](const std::string& id, bool h) { plug.Report(id, h); }, nullptr);
+  const Response probe = api.Probe();
+  // a fault report and its recovery must each produce exactly one resend
+  const std::string first_id = dm.m["nvidia.com/gpu"].GetIDs().front();
+  plug.Report(first_id, false);
+  plug.Report(first_id, false);
+  plug.Report(first_id, true);
+  plug.Stop();
+  law.join();
+  const Response unknown = api.Probe("GPU-00000000-0000-0000-0000-000000000000");
+  const std::string m = api.Metrics().body;
+
+  printf("{\"devices\":%d,\"unhealthy\":%d,\"lists\":[", n, unhealthy);
+  for (size_t i = 0; i < lists.size(); ++i) printf("%s%s", i ? "," : "", lists[i].c_str());
+  printf("],\"probe\":%s,\"unknown\":%s,\"version\":%s,\"health\":%s,\"log\":[", probe.body.c_str(), unknown.body.c_str(),
+         api.Version().body.c_str(), api.Health().body.c_str());
+  for (size_t i = 0; i < log.size(); ++i) printf("%s\"%s\"", i ? "," : "", jsonEscape(log[i]).c_str());
+  printf("],\"metrics\":\"%s\"}\n", jsonEscape(m).c_str());
+  return 0;
+}

@@ -10,6 +10,11 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module")
 def mp():
+    # libgpuprobe dlopens "libnccl.so.2" and reuses whichever copy the process already holds.
+    # torch bundles a newer NCCL under the same soname; if the system copy were loaded first, a
+    # later `import torch` in this pytest process would bind to it and fail on a missing symbol.
+    # Importing torch first makes its copy the process-wide one (bench.py does the same).
+    import torch  # noqa: F401
     p = gpuprobe.Probe(keep_arena=1)
     yield p
     p.close()
