@@ -99,6 +99,7 @@ int device_prepare(Ctx* ctx, Device* d) {
   d->h_count = reinterpret_cast<unsigned long long*>(d->h_results + kMaxResults);
   for (int i = 0; i < kEventPool; ++i) CU_OR_RETURN(cudaEventCreate(&d->events[i]), nullptr);
   CU_OR_RETURN(stream_kernels_configure(), nullptr);
+  if (d->cc_major == 10) CU_OR_RETURN(gemm_kernels_configure(), nullptr);
   CU_OR_RETURN(cudaStreamSynchronize(d->stream), nullptr);
   d->ready = true;
   return GP_OK;
@@ -337,6 +338,21 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
     return code;
   };
 
+  {
+    // one allocation for the whole call: the largest arena any selected probe needs
+    uint64_t need = 0;
+    if (mask & GP_PROBE_COPY) need = std::max<uint64_t>(need, 2 * hbm);
+    if (mask & GP_PROBE_TRIAD) need = std::max<uint64_t>(need, 3 * hbm);
+    if (mask & GP_PROBE_PATTERN) need = std::max<uint64_t>(need, pat);
+    if (mask & GP_PROBE_GEMM) {
+      const uint64_t g = ctx->cfg.gemm_mnk ? ctx->cfg.gemm_mnk : 8192;
+      need = std::max<uint64_t>(need, 8 * g * g + (4ull << 20));  // A + B (2 B) + C (4 B) + check vectors
+    }
+    if (need > d->arena_bytes && need <= cfg_arena_cap(ctx)) {
+      rc = ensure_arena(ctx, d, need);
+      if (rc) return fail(rc);
+    }
+  }
   if (mask & GP_PROBE_COPY) {
     rc = copy_probe_locked(ctx, d, hbm, warmup, iters, &out->copy_t, &out->copy_checksum, &out->copy_ok, &out->detail);
     if (rc) return fail(rc);

@@ -422,13 +422,6 @@ template <int CG>
 static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, float* C, int M, int N,
                                   int K, int sm_count, cudaStream_t stream) {
   using Cfg = GemmCfg<CG>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)Cfg::kSmemBytes);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
   const int tiles = (M / Cfg::kTileM) * (N / kTileN);
   int units = std::min(tiles, sm_count / CG);
   cudaLaunchConfig_t cfg = {};
@@ -444,6 +437,15 @@ static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, 
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, C, M, N, K);
+}
+
+// function attributes are per device: called once from device_prepare with the device current
+cudaError_t gemm_kernels_configure() {
+  cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)GemmCfg<1>::kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(gemm_bf16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)GemmCfg<2>::kSmemBytes);
 }
 
 struct GemmPlan {

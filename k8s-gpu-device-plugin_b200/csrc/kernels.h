@@ -51,5 +51,6 @@ cudaError_t launch_gen_bf16(uint16_t* dst, uint64_t n, uint64_t seed, int sm_cou
 cudaError_t launch_triad_check(const float* a, uint64_t n, uint64_t seed, float s,
                                unsigned long long* d_count, int sm_count, cudaStream_t stream);
 cudaError_t stream_kernels_configure();  // opt-in dynamic smem; call once per device
+cudaError_t gemm_kernels_configure();    // same, for the tcgen05 kernels (sm_100 devices only)
 
 }  // namespace gp
