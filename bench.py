@@ -325,18 +325,28 @@ def run_ours(args):
                 "achieved_gbps": ach, "frac_of_measured_peak": ach / peak, "frac_of_8tbps": ach / 8000.0,
                 "share_of_step": s.total_ms / dev_ms if dev_ms else None}
     dom = max(kernels, key=lambda k: kernels[k]["share_of_step"])
-    traffic = None
+    traffic, traffic_note = None, None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get(dom)
+            tj = json.load(f).get(dom)
+        alg = {"copy": 2, "triad": 3, "fill": 1, "verify": 1}[dom] * nbytes
+        key = f"dram_bytes_per_launch_at_{nbytes}"
+        if tj and key in tj:
+            traffic, traffic_note = tj[key], tj.get("source_full_size")
+        elif tj:
+            traffic = tj["ratio_traffic_over_algorithmic"] * alg
+            traffic_note = ("ncu capture at 2 GiB per array scaled by size: measured traffic/algorithmic = "
+                            f"{tj['ratio_traffic_over_algorithmic']:.4f}; " + tj.get("source", ""))
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbps"], "peak": peak,
                 "unit": "GB/s", "frac": kernels[dom]["achieved_gbps"] / peak, "traffic": traffic,
+                "traffic_note": traffic_note,
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": {"copy": 2 * nbytes, "triad": 3 * nbytes,
                                                  "fill": nbytes, "verify": nbytes}[dom]}
-    gpu_launches = sum(int(stats[i].launches) for i in range(7))
+    # every verify is two kernels (chunk grid + one-CTA finalize): 10 launches per step
+    gpu_launches = sum(int(stats[i].launches) for i in range(7)) + int(stats[gpuprobe.GP_K_VERIFY].launches)
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,

@@ -1,0 +1,12 @@
+#!/usr/bin/env python3
+"""Runs only the GEMM probe (for ncu captures): python tools/gemm_only.py [mnk] [iters]"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "k8s-gpu-device-plugin_b200"))
+import gpuprobe
+mnk = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+iters = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+with gpuprobe.Probe(keep_arena=1) as p:
+    g = p.gemm_probe("0", mnk=mnk, iters=iters, warmup=2, samples=1024)
+    print(f"gemm {mnk}^3: best {g.tflops_best:.1f} median {g.tflops_median:.1f} TFLOP/s, best {g.t.best_ms:.4f} ms, "
+          f"err {g.max_scaled_err:.2e}, freivalds {g.freivalds_err:.2e}, bad {g.samples_bad}")
