@@ -186,11 +186,19 @@ def run_ours(args):
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    # a host-side barrier for the sweep leg: an NCCL barrier would park a spinning kernel on
+    # every waiting rank's GPU while rank 0 grades those same GPUs
+    cpu_group = dist.new_group(backend="gloo") if dist is not None else None
 
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def host_barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier(group=cpu_group)
 
     nbytes = args.bytes
     nwords = nbytes // 8
@@ -278,7 +286,7 @@ def run_ours(args):
     sweep = None
     if not args.no_sweep:
         p2.trim()
-        barrier()
+        host_barrier()
         if rank == 0:
             p3 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
             try:
@@ -304,7 +312,7 @@ def run_ours(args):
                 except gpuprobe.GpuProbeError as e2:
                     sweep = {"error": str(e2)}
             p3.close()
-        barrier()
+        host_barrier()
     p2.close()
 
     if rank != 0:
