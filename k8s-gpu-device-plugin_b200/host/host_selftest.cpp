@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <thread>
 
+#include "manager.hpp"
 #include "router.hpp"
 
 using namespace plugin;
@@ -131,6 +132,81 @@ int main() {
   CHECK(reports == 1 + 5 && all.body.find("MIG-0") != std::string::npos);
   CHECK(api.Probe("GPU-none").body == "{\"code\":404,\"data\":null,\"msg\":\"unknown device GPU-none\"}");
   CHECK(Failed(7, "a\"b").find("a\\\"b") != std::string::npos);
+
+  // --- NewDeviceMap / strategies / error text (device/device_map.go:24-98) ---
+  auto mkinfo = [](const std::string& u) { auto p = std::make_shared<FakeInfo>(); p->uuid = u; return p; };
+  std::vector<GpuNode> nodes;
+  for (int i = 0; i < 3; ++i) nodes.push_back({i, "NVIDIA B200", false, mkinfo("GPU-n" + std::to_string(i)), {}});
+  nodes[2].migEnabled = true;
+  nodes[2].migs = {{0, "1g.23gb", mkinfo("MIG-a")}, {1, "1g.23gb", mkinfo("MIG-b")}, {2, "7g.180gb", mkinfo("MIG-c")}};
+  {
+    auto [m1, e1] = NewDeviceMap(nodes, {Resource::New("*", "gpu")}, MigStrategyNone);
+    CHECK(!e1 && m1.m["nvidia.com/gpu"].size() == 3);                       // none: MIG-enabled GPUs stay whole
+    auto [m2, e2] = NewDeviceMap(nodes, {Resource::New("*", "gpu")}, MigStrategySingle);
+    CHECK(!e2 && m2.m["nvidia.com/gpu"].size() == 2);                       // single: MIG-enabled GPU skipped
+    auto [m3, e3] = NewDeviceMap(nodes, {Resource::New("1g.23gb", "mig-1g.23gb"), Resource::New("7g.180gb", "mig-7g.180gb")}, MigStrategyMixed);
+    CHECK(!e3 && m3.m["nvidia.com/mig-1g.23gb"].size() == 2 && m3.m["nvidia.com/mig-7g.180gb"].GetByIndex("2:2"));
+    auto [m4, e4] = NewDeviceMap(nodes, {Resource::New("1g.23gb", "mig-1g.23gb")}, MigStrategyMixed);
+    CHECK(e4 && *e4 == "MIG profile '7g.180gb' does not match any resource patterns");
+    auto [m5, e5] = NewDeviceMap(nodes, {Resource::New("GPU", "nvidia.com/gpu")}, MigStrategyNone);  // the reference's own pattern
+    CHECK(e5 && *e5 == "GPU name 'NVIDIA B200' does not match any resource patterns");
+    auto [m6, e6] = NewDeviceMap(nodes, {}, "weird");
+    CHECK(e6 && *e6 == "invalid MIG strategy: weird");
+    (void)m4; (void)m5; (void)m6;
+  }
+  // --- mig-minors parser (device/mig.go) ---
+  {
+    auto caps = GetMigCapabilityDevicePaths("config 1\nmonitor 2\ngpu0/gi1/access 12\ngpu0/gi1/ci0/access 13\ngarbage line\n");
+    CHECK(caps.size() == 4 && caps["/proc/driver/nvidia/capabilities/gpu0/mig/gi1/ci0/access"] == "/dev/nvidia-caps/nvidia-cap13");
+    CHECK(caps["/proc/driver/nvidia/capabilities/gpu0/mig/gi1/access"] == "/dev/nvidia-caps/nvidia-cap12" && caps["/proc/driver/nvidia/capabilities/mig/config"] == "/dev/nvidia-caps/nvidia-cap1");
+  }
+  // --- PluginManager: grade inside loadPlugins, Restart flag, Reprobe feeds ListAndWatch, ticker ---
+  {
+    FakeBackend fb;
+    fb.bad = {"GPU-n1"};
+    ProbeMetrics pm;
+    PluginManager mgr(MigStrategySingle, {Resource::New("*", "gpu")}, [&] { return nodes; }, &fb, &pm, GP_PROBE_ALL_SINGLE);
+    CHECK(!mgr.loadPlugins() && mgr.loads() == 1 && mgr.unhealthyAtLoad() == 1 && mgr.plugins().size() == 1);
+    auto plug0 = mgr.plugins()[0];
+    std::vector<std::vector<PluginDevice>> got;
+    std::thread t([&] { plug0->ListAndWatch([&](const std::vector<PluginDevice>& l) { got.push_back(l); return true; }); });
+    fb.bad = {"GPU-n0"};                        // n1 recovers, n0 breaks
+    auto [graded, re] = mgr.Reprobe();
+    CHECK(!re && graded.size() == 2);
+    CHECK(mgr.Reprobe("GPU-zzz").second.value() == "unknown device GPU-zzz");
+    plug0->Stop();
+    t.join();
+    CHECK(got.size() == 3);                     // first list + two transitions
+    CHECK(health_of(got[0], "GPU-n1") == "Unhealthy" && health_of(got[2], "GPU-n1") == "Healthy" && health_of(got[2], "GPU-n0") == "Unhealthy");
+    CHECK(pm.Render().find("gpu_probe_healthy{index=\"0\",uuid=\"GPU-n0\"} 0") != std::string::npos);
+    mgr.Restart();
+    CHECK(!mgr.poll() && mgr.loads() == 2 && !mgr.poll() && mgr.loads() == 2);   // flag consumed once
+    const int before = mgr.reprobes();
+    mgr.StartTicker(std::chrono::milliseconds(5));
+    std::this_thread::sleep_for(std::chrono::milliseconds(80));
+    mgr.StopTicker();
+    CHECK(mgr.reprobes() >= before + 3);
+    PluginManager bad(MigStrategyNone, {Resource::New("GPU", "gpu")}, [&] { return nodes; }, &fb, &pm, 1);
+    CHECK(bad.loadPlugins().value() == "GPU name 'NVIDIA B200' does not match any resource patterns");
+  }
+  // --- preferred allocation ---
+  {
+    Devices reps;
+    for (const char* id : {"GPU-a::0", "GPU-a::1", "GPU-b::0", "GPU-b::1"}) { auto d = std::make_shared<Device>(); d->ID = id; reps.m[id] = d; }
+    auto [alloc, ae2] = distributedAlloc(reps, {"GPU-a::0", "GPU-a::1", "GPU-b::0", "GPU-b::1"}, {}, 2);
+    CHECK(!ae2 && alloc.size() == 2 && AnnotatedID{alloc[0]}.GetID() != AnnotatedID{alloc[1]}.GetID());  // spread over both GPUs
+    CHECK(distributedAlloc(reps, {"GPU-a::0"}, {}, 2).second.value() == "not enough available devices to satisfy allocation");
+    auto [withreq, ae3] = distributedAlloc(reps, {"GPU-a::0", "GPU-a::1", "GPU-b::0"}, {"GPU-a::0"}, 2);
+    CHECK(!ae3 && withreq.size() == 2 && withreq[0] == "GPU-a::0" && withreq[1] != "GPU-a::0");  // required first; tie broken as the reference does
+    std::vector<std::string> u4 = {"G0", "G1", "G2", "G3"};
+    std::vector<double> bw(16, 780.0);
+    bw[0 * 4 + 1] = bw[1 * 4 + 0] = 90.0;       // a degraded 0<->1 link
+    auto [pick, pe] = alignedAllocFromMatrix(u4, bw, u4, {"G0"}, 3);
+    CHECK(!pe && pick.size() == 3 && pick[0] == "G0" && std::find(pick.begin(), pick.end(), "G1") == pick.end());
+    auto [flat, fe] = alignedAllocFromMatrix(u4, std::vector<double>(16, 780.0), u4, {}, 2);
+    CHECK(!fe && flat == std::vector<std::string>({"G0", "G1"}));
+    CHECK(alignedAllocFromMatrix(u4, bw, {"G0"}, {}, 2).second.has_value());
+  }
   printf("host_selftest ok\n");
   return 0;
 }

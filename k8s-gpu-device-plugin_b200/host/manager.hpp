@@ -1,0 +1,265 @@
+// manager.hpp — the rest of the reference's host path around the probe:
+//   NewDeviceMap / build / buildGPUDeviceMap / buildMigDeviceMap   <- device/device_map.go:24-98
+//   GetMigCapabilityDevicePaths (line parser)                       <- device/mig.go:20-81
+//   PluginManager loadPlugins / restartPlugins / Restart            <- plugin/manager.go:102-194
+//   distributedAlloc                                                <- plugin/plugin.go:284-326
+//   preferred allocation from the MEASURED P2P matrix (replaces the NVML link query of
+//   alignedAlloc, plugin/plugin.go:256-282, whose nvmllib is never set — SURVEY.md §8f.3)
+// What is new: grading inside loadPlugins (before anything is advertised), Reprobe, a ticker.
+// The kubelet socket, gRPC server and fsnotify watcher are transport and are not mirrored.
+#pragma once
+#include <algorithm>
+#include <cstdio>
+#include <sstream>
+
+#include "metrics.hpp"
+#include "probe.hpp"
+
+namespace plugin {
+
+// resource/resource.go:15-40
+inline const char* const MigStrategyNone = "none";
+inline const char* const MigStrategySingle = "single";
+inline const char* const MigStrategyMixed = "mixed";
+struct Resource {
+  std::string Pattern, Name;
+  static Resource New(const std::string& pattern, std::string name) {  // resource.go:31-40
+    if (name.rfind("nvidia.com/", 0) != 0) name = "nvidia.com/" + name;
+    return {pattern, name};
+  }
+};
+
+// What go-nvlib's VisitDevices / VisitMigDevices hand to the builder (device_map.go:50,80)
+struct MigNode {
+  int j;
+  std::string profile;  // MigProfile.String(), e.g. "1g.23gb"
+  std::shared_ptr<deviceInfo> info;
+};
+struct GpuNode {
+  int i;
+  std::string name;  // gpu.GetName()
+  bool migEnabled = false;
+  std::shared_ptr<deviceInfo> info;
+  std::vector<MigNode> migs;
+};
+
+// device_map.go:24-98
+inline std::pair<DeviceMap, Error> NewDeviceMap(const std::vector<GpuNode>& gpus, const std::vector<Resource>& resources,
+                                                const std::string& migStrategy) {
+  DeviceMap devices;
+  if (migStrategy == MigStrategyNone || migStrategy == MigStrategySingle) {  // buildGPUDeviceMap :48-75
+    for (const auto& gpu : gpus) {
+      if (gpu.migEnabled && migStrategy != MigStrategyNone) continue;
+      bool matched = false;
+      for (const auto& r : resources) {
+        if (matchResourcePattern(r.Pattern, gpu.name)) {
+          if (auto e = devices.setEntry(r.Name, std::to_string(gpu.i), *gpu.info)) return {devices, e};
+          matched = true;
+          break;
+        }
+      }
+      if (!matched) return {devices, "GPU name '" + gpu.name + "' does not match any resource patterns"};
+    }
+    return {devices, std::nullopt};
+  }
+  if (migStrategy == MigStrategyMixed) {  // buildMigDeviceMap :78-98
+    for (const auto& gpu : gpus)
+      for (const auto& mig : gpu.migs) {
+        bool matched = false;
+        for (const auto& r : resources) {
+          if (matchResourcePattern(r.Pattern, mig.profile)) {
+            if (auto e = devices.setEntry(r.Name, std::to_string(gpu.i) + ":" + std::to_string(mig.j), *mig.info)) return {devices, e};
+            matched = true;
+            break;
+          }
+        }
+        if (!matched) return {devices, "MIG profile '" + mig.profile + "' does not match any resource patterns"};
+      }
+    return {devices, std::nullopt};
+  }
+  return {devices, "invalid MIG strategy: " + migStrategy};
+}
+
+// device/mig.go:38-66: one line of /proc/driver/nvidia-caps/mig-minors -> (capability path, minor)
+inline std::optional<std::pair<std::string, int>> parseMigMinorsLine(const std::string& line) {
+  int gpu, gi, ci, minor;
+  const std::string caps = "/proc/driver/nvidia/capabilities";
+  if (sscanf(line.c_str(), "gpu%d/gi%d/ci%d/access %d", &gpu, &gi, &ci, &minor) == 4)
+    return {{caps + "/gpu" + std::to_string(gpu) + "/mig/gi" + std::to_string(gi) + "/ci" + std::to_string(ci) + "/access", minor}};
+  if (sscanf(line.c_str(), "gpu%d/gi%d/access %d", &gpu, &gi, &minor) == 3)
+    return {{caps + "/gpu" + std::to_string(gpu) + "/mig/gi" + std::to_string(gi) + "/access", minor}};
+  if (sscanf(line.c_str(), "config %d", &minor) == 1) return {{caps + "/mig/config", minor}};
+  if (sscanf(line.c_str(), "monitor %d", &minor) == 1) return {{caps + "/mig/monitor", minor}};
+  return std::nullopt;  // "unparsable line": skipped, as the reference logs and continues
+}
+inline std::map<std::string, std::string> GetMigCapabilityDevicePaths(const std::string& minorsText) {
+  std::map<std::string, std::string> out;
+  std::istringstream in(minorsText);
+  std::string line;
+  while (std::getline(in, line))
+    if (auto p = parseMigMinorsLine(line)) out[p->first] = "/dev/nvidia-caps/nvidia-cap" + std::to_string(p->second);
+  return out;
+}
+
+// plugin/plugin.go:284-326 — spread an allocation over replicated GPUs, least-used first
+inline std::pair<std::vector<std::string>, Error> distributedAlloc(const Devices& all, const std::vector<std::string>& available,
+                                                                   const std::vector<std::string>& required, int size) {
+  std::vector<std::string> candidates = all.Subset(available).Difference(all.Subset(required)).GetIDs();
+  const int needed = size - (int)required.size();
+  if ((int)candidates.size() < needed) return {{}, "not enough available devices to satisfy allocation"};
+  struct Cnt { int total = 0, available = 0; };
+  std::map<std::string, Cnt> replicas;
+  for (const auto& c : candidates) replicas[AnnotatedID{c}.GetID()].available++;
+  for (const auto& kv : all.m) {
+    const std::string id = AnnotatedID{kv.first}.GetID();
+    if (replicas.count(id)) replicas[id].total++;
+  }
+  std::vector<std::string> devices;
+  for (int i = 0; i < needed; ++i) {
+    std::stable_sort(candidates.begin(), candidates.end(), [&](const std::string& a, const std::string& b) {
+      const Cnt& ca = replicas[AnnotatedID{a}.GetID()];
+      const Cnt& cb = replicas[AnnotatedID{b}.GetID()];
+      return ca.total - ca.available < cb.total - cb.available;
+    });
+    replicas[AnnotatedID{candidates[0]}.GetID()].available--;
+    devices.push_back(candidates[0]);
+    candidates.erase(candidates.begin());
+  }
+  std::vector<std::string> out(required);
+  out.insert(out.end(), devices.begin(), devices.end());
+  return {out, std::nullopt};
+}
+
+// Preferred allocation from the measured P2P matrix: greedily grow the required set with the
+// candidate whose WORST measured link to the set is best (ties: lowest id).  On a healthy
+// NVSwitch box the matrix is flat and this is id order; with a degraded link it steers around it.
+inline std::pair<std::vector<std::string>, Error> alignedAllocFromMatrix(
+    const std::vector<std::string>& uuidByOrdinal, const std::vector<double>& gbps /*n*n, row=src*/,
+    const std::vector<std::string>& available, const std::vector<std::string>& required, int size) {
+  const int n = (int)uuidByOrdinal.size();
+  auto ord = [&](const std::string& id) { for (int i = 0; i < n; ++i) if (uuidByOrdinal[(size_t)i] == id) return i; return -1; };
+  std::vector<std::string> chosen(required);
+  std::vector<std::string> cand;
+  for (const auto& a : available)
+    if (std::find(required.begin(), required.end(), a) == required.end()) cand.push_back(a);
+  std::sort(cand.begin(), cand.end());
+  if ((int)(chosen.size() + cand.size()) < size) return {{}, "not enough available devices to satisfy allocation"};
+  auto link = [&](const std::string& a, const std::string& b) {
+    const int i = ord(a), j = ord(b);
+    if (i < 0 || j < 0 || (int)gbps.size() < n * n) return 0.0;
+    return std::min(gbps[(size_t)(i * n + j)], gbps[(size_t)(j * n + i)]);
+  };
+  while ((int)chosen.size() < size) {
+    int best = -1;
+    double best_score = -1;
+    for (int c = 0; c < (int)cand.size(); ++c) {
+      double worst = 1e30;
+      for (const auto& s : chosen) worst = std::min(worst, link(cand[(size_t)c], s));
+      if (chosen.empty()) {  // seed with the device whose weakest link overall is strongest
+        worst = 1e30;
+        for (const auto& o : cand) if (o != cand[(size_t)c]) worst = std::min(worst, link(cand[(size_t)c], o));
+      }
+      if (worst > best_score) { best_score = worst; best = c; }
+    }
+    chosen.push_back(cand[(size_t)best]);
+    cand.erase(cand.begin() + best);
+  }
+  return {chosen, std::nullopt};
+}
+
+// plugin/manager.go:20-194 without the sockets: owns the device map and one plugin per resource.
+class PluginManager {
+ public:
+  using Enumerate = std::function<std::vector<GpuNode>()>;
+  PluginManager(std::string migStrategy, std::vector<Resource> resources, Enumerate enumerate, ProbeBackend* be,
+                ProbeMetrics* metrics, uint32_t mask)
+      : migStrategy_(std::move(migStrategy)), resources_(std::move(resources)), enumerate_(std::move(enumerate)),
+        be_(be), metrics_(metrics), mask_(mask) {}
+  ~PluginManager() { StopTicker(); }
+
+  // manager.go:156-174, plus the grade: kubelet never sees an ungraded device
+  Error loadPlugins() {
+    auto [dm, err] = NewDeviceMap(enumerate_(), resources_, migStrategy_);
+    if (err) return err;
+    std::lock_guard<std::mutex> g(mu_);
+    devices_ = std::move(dm);
+    unhealthy_at_load_ = GradeDevices(devices_, *be_, mask_, &log_);
+    for (auto& d : devices_.All()) metrics_->Update(*d);
+    plugins_.clear();
+    for (auto& kv : devices_.m) plugins_.push_back(std::make_shared<NvidiaDevicePlugin>(kv.first, kv.second));
+    ++loads_;
+    return std::nullopt;
+  }
+  // manager.go:108-110 sets a flag that the Start loop polls (manager.go:93-97); here the poll is explicit
+  void Restart() { restart_ = true; }
+  Error poll() {
+    if (!restart_.exchange(false)) return std::nullopt;
+    return restartPlugins();
+  }
+  Error restartPlugins() {  // manager.go:177-194
+    { std::lock_guard<std::mutex> g(mu_); for (auto& p : plugins_) p->Stop(); plugins_.clear(); devices_ = DeviceMap(); }
+    return loadPlugins();
+  }
+  // re-grade (all, or one uuid) while streams are open: transitions go through Report
+  std::pair<std::vector<std::shared_ptr<Device>>, Error> Reprobe(const std::string& uuid = "") {
+    std::lock_guard<std::mutex> g(mu_);
+    DeviceMap scope;
+    for (auto& kv : devices_.m)
+      for (auto& dv : kv.second.m)
+        if (uuid.empty() || dv.second->GetUUID() == uuid) scope.m[kv.first].m[dv.first] = dv.second;
+    if (scope.m.empty()) return {{}, "unknown device " + uuid};
+    GradeDevices(scope, *be_, mask_, &log_, /*apply_health=*/false);
+    auto all = scope.All();
+    for (auto& d : all) {
+      metrics_->Update(*d);
+      for (auto& p : plugins_) if (p->devices().GetByID(d->ID)) p->Report(d->ID, VerdictHealthy(*d));
+    }
+    ++reprobes_;
+    return {all, std::nullopt};
+  }
+  void StartTicker(std::chrono::milliseconds interval) {
+    StopTicker();
+    ticking_ = true;
+    ticker_ = std::thread([this, interval] {
+      std::unique_lock<std::mutex> lk(tick_mu_);
+      while (ticking_) {
+        if (tick_cv_.wait_for(lk, interval, [this] { return !ticking_; })) break;
+        lk.unlock();
+        Reprobe("");
+        lk.lock();
+      }
+    });
+  }
+  void StopTicker() {
+    { std::lock_guard<std::mutex> g(tick_mu_); ticking_ = false; }
+    tick_cv_.notify_all();
+    if (ticker_.joinable()) ticker_.join();
+  }
+  std::vector<std::shared_ptr<NvidiaDevicePlugin>> plugins() { std::lock_guard<std::mutex> g(mu_); return plugins_; }
+  DeviceMap& devices() { return devices_; }
+  int loads() const { return loads_; }
+  int reprobes() const { return reprobes_; }
+  int unhealthyAtLoad() const { return unhealthy_at_load_; }
+  std::vector<std::string> log() { std::lock_guard<std::mutex> g(mu_); return log_; }
+
+ private:
+  std::string migStrategy_;
+  std::vector<Resource> resources_;
+  Enumerate enumerate_;
+  ProbeBackend* be_;
+  ProbeMetrics* metrics_;
+  uint32_t mask_;
+  std::mutex mu_;
+  DeviceMap devices_;
+  std::vector<std::shared_ptr<NvidiaDevicePlugin>> plugins_;
+  std::vector<std::string> log_;
+  std::atomic<bool> restart_{false};
+  std::atomic<int> loads_{0}, reprobes_{0};
+  int unhealthy_at_load_ = 0;
+  std::thread ticker_;
+  std::mutex tick_mu_;
+  std::condition_variable tick_cv_;
+  bool ticking_ = false;
+};
+
+}  // namespace plugin
