@@ -108,6 +108,16 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
+def max_over_ranks(dist, values, device):
+    """MAX over ranks of a list of floats (device-timed intervals); identity when not distributed."""
+    if dist is None:
+        return list(values)
+    import torch
+    t = torch.tensor(list(values), dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t]
+
+
 def dist_env():
     return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
             int(os.environ.get("WORLD_SIZE", "1")))
@@ -236,11 +246,7 @@ def run_ours(args):
     stats = probe.kernel_stats(dev)
     dev_ms = stats[gpuprobe.GP_K_STEP].total_ms
 
-    wall_max, dev_ms_max = wall, dev_ms
-    if dist is not None:
-        t = torch.tensor([wall, dev_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        wall_max, dev_ms_max = float(t[0]), float(t[1])
+    wall_max, dev_ms_max = max_over_ranks(dist, [wall, dev_ms], "cuda")
 
     e2e = None
     if args.no_e2e:
@@ -267,10 +273,7 @@ def run_ours(args):
         e2e_bytes = sum(st2[i].algo_bytes for i in (gpuprobe.GP_K_COPY, gpuprobe.GP_K_TRIAD,
                                                     gpuprobe.GP_K_FILL, gpuprobe.GP_K_VERIFY))
         e2e_launches = sum(int(st2[i].launches) for i in range(7))
-        if dist is not None:
-            t = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_wall = float(t[0])
+        e2e_wall = max_over_ranks(dist, [e2e_wall], "cuda")[0]
         d2h = ctypes.sizeof(gpuprobe.DeviceResult) + last.pattern_passes * 48 + 48 + 8
         e2e = {"value": e2e_bytes * n_gpus / e2e_wall / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h,
