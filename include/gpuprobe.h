@@ -296,7 +296,10 @@ int gp_inject_bitflip(gp_ctx* ctx, const char* uuid, uint64_t word_index, int bi
 
 /* dir: 0 = read (kernel on src loads from dst's memory), 1 = write (kernel on
  * src stores to dst), 2 = bidirectional write (src->dst and dst->src at once).
- * gbps is n*n row-major, row = src; diagonal = local bandwidth. */
+ * gbps is n*n row-major, row = src; diagonal = local bandwidth.
+ * dir 3 = all pairs at once (switch saturation): every GPU reads `bytes` from
+ * each peer concurrently; row i = GPU i's aggregate ingress / (n-1), diagonal =
+ * the aggregate. */
 int gp_probe_p2p(gp_ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps);
 /* In-place fp32 sum ncclAllReduce over the first nranks devices. */
 int gp_probe_allreduce(gp_ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters,

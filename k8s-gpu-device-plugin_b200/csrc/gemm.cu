@@ -187,7 +187,7 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
 template <int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 float* __restrict__ C, int M, int N, int K) {
+                 float* __restrict__ C, int M, int N, int K, int group_m) {
   using Cfg = GemmCfg<CG>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle-128B needs 1024-byte alignment
@@ -228,12 +228,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
   // raster: groups of kGroupM tile rows, columns fastest inside a group, so that the ~148 tiles
   // in flight share A and B panels that fit in L2 together
-  constexpr int kGroupM = 16 / CG;
   auto tile_coords = [&](int t, int& tm, int& tn) {
-    const int per_group = kGroupM * tiles_n;
+    const int per_group = group_m * tiles_n;
     const int g = t / per_group, r = t % per_group;
-    const int rows = min(kGroupM, tiles_m - g * kGroupM);
-    tm = g * kGroupM + r % rows;
+    const int rows = min(group_m, tiles_m - g * group_m);
+    tm = g * group_m + r % rows;
     tn = r / rows;
   };
 
@@ -436,7 +435,10 @@ static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, C, M, N, K);
+  // raster group height in tile rows (development override: GPUPROBE_GEMM_GROUP_M)
+  static const int env_group = getenv("GPUPROBE_GEMM_GROUP_M") ? atoi(getenv("GPUPROBE_GEMM_GROUP_M")) : 0;
+  const int group_m = env_group > 0 ? env_group : 16 / CG;
+  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, C, M, N, K, group_m);
 }
 
 // function attributes are per device: called once from device_prepare with the device current

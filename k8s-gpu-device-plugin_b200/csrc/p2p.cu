@@ -99,6 +99,34 @@ p2p_write_np_kernel(u64x4* __restrict__ peer, uint64_t nvec, uint64_t tag) {
   }
 }
 
+// all-pairs-at-once: one kernel on `src` reads from EVERY peer concurrently (CTA b -> peer b % npeers),
+// the switch-saturation round of SURVEY.md §8(e)
+struct PeerTable {
+  const u64x4* p[8];
+  int n;
+};
+__global__ void __launch_bounds__(kP2PThreads)
+p2p_read_all_kernel(PeerTable t, uint64_t nvec_per_peer, unsigned long long* __restrict__ sink) {
+  const int peer = blockIdx.x % t.n;
+  const uint64_t cta = blockIdx.x / t.n, ctas = gridDim.x / t.n;
+  const u64x4* __restrict__ base = t.p[peer];
+  const uint64_t stride = ctas * kP2PThreads;
+  uint64_t acc = 0;
+  uint64_t g = cta * kP2PThreads + threadIdx.x;
+  for (; g + (kP2PUnroll - 1) * stride < nvec_per_peer; g += kP2PUnroll * stride) {
+    u64x4 v[kP2PUnroll];
+#pragma unroll
+    for (int u = 0; u < kP2PUnroll; ++u) v[u] = ld256_stream(base + g + u * stride);
+#pragma unroll
+    for (int u = 0; u < kP2PUnroll; ++u) acc += (v[u].v[0] ^ v[u].v[1]) + (v[u].v[2] ^ v[u].v[3]);
+  }
+  for (; g < nvec_per_peer; g += stride) {
+    const u64x4 v = ld256_stream(base + g);
+    acc += (v.v[0] ^ v.v[1]) + (v.v[2] ^ v.v[3]);
+  }
+  if (acc == 0x9E3779B97F4A7C15ull) atomicAdd(sink, 1ull);
+}
+
 __global__ void p2p_check_kernel(const u64x4* __restrict__ buf, uint64_t nvec, uint64_t tag,
                                  unsigned long long* __restrict__ bad) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -220,6 +248,47 @@ int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
       if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, "cudaDeviceEnablePeerAccess", nullptr);
       (void)cudaGetLastError();
     }
+  }
+  if (dir == 3) {
+    // every GPU reads `bytes` from each of its n-1 peers at once; row i holds GPU i's aggregate
+    // ingress divided evenly over its peers, the diagonal holds the aggregate itself
+    if (ngpus < 2 || ngpus > 9) { set_error("all-at-once mode needs 2..9 GPUs"); return GP_ERR_INVALID; }
+    const uint64_t nvec = bytes / 32;
+    std::vector<float> best((size_t)ngpus, 1e30f);
+    for (int it = 0; it < 4; ++it) {
+      for (int i = 0; i < ngpus; ++i) {
+        Device* s = ctx->devs[(size_t)i].get();
+        PeerTable t{};
+        for (int j = 0; j < ngpus; ++j)
+          if (j != i) t.p[t.n++] = reinterpret_cast<const u64x4*>(ctx->devs[(size_t)j]->arena);
+        CU_OR_RETURN(cudaSetDevice(i));
+        CU_OR_RETURN(cudaEventRecord(s->events[0], s->stream));
+        const int ctas_per_peer = std::max(1, s->sm_count * 4 / t.n);
+        p2p_read_all_kernel<<<ctas_per_peer * t.n, kP2PThreads, 0, s->stream>>>(t, nvec, s->d_count);
+        CU_OR_RETURN(cudaGetLastError());
+        CU_OR_RETURN(cudaEventRecord(s->events[1], s->stream));
+      }
+      for (int i = 0; i < ngpus; ++i) {
+        Device* s = ctx->devs[(size_t)i].get();
+        CU_OR_RETURN(cudaSetDevice(i));
+        CU_OR_RETURN(cudaStreamSynchronize(s->stream));
+        float ms = 0;
+        CU_OR_RETURN(cudaEventElapsedTime(&ms, s->events[0], s->events[1]));
+        if (it > 0) {
+          best[(size_t)i] = std::min(best[(size_t)i], ms);
+          s->stats[GP_K_P2P].launches += 1;
+          s->stats[GP_K_P2P].total_ms += ms;
+          s->stats[GP_K_P2P].algo_bytes += (double)bytes * (ngpus - 1);
+        }
+      }
+    }
+    for (int i = 0; i < ngpus; ++i) {
+      const double agg = (double)bytes * (ngpus - 1) / (best[(size_t)i] * 1e-3) / 1e9;
+      for (int j = 0; j < ngpus; ++j) gbps[i * ngpus + j] = i == j ? agg : agg / (ngpus - 1);
+    }
+    if (!ctx->cfg.keep_arena)
+      for (int i = 0; i < ngpus; ++i) free_arena(ctx->devs[(size_t)i].get());
+    return GP_OK;
   }
   const bool write = dir != 0;
   const int iters = 3;

@@ -67,6 +67,9 @@ def test_p2p_matrix_pairs(mp):
         assert min(off) > 100, (direction, m)          # NVLink, not PCIe
         assert max(off) < 1000, (direction, m)         # not above the 900 GB/s/direction link
         assert min(off) > 0.6 * max(off), (direction, m)  # NVSwitch: flat off-diagonal
+    m = mp.probe_p2p(n, 256 << 20, 3)  # all pairs at once: aggregate ingress per GPU on the diagonal
+    for i in range(n):
+        assert 100 < m[i][i] < 1000 and abs(m[i][(i + 1) % n] * (n - 1) - m[i][i]) < 1e-6 * m[i][i]
     with pytest.raises(gpuprobe.GpuProbeError):
         mp.probe_p2p(n + 1, 1 << 20, 0)
 
