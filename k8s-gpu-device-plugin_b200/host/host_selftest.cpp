@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <thread>
 
+#include "config.hpp"
 #include "manager.hpp"
 #include "router.hpp"
 
@@ -206,6 +207,21 @@ int main() {
     auto [flat, fe] = alignedAllocFromMatrix(u4, std::vector<double>(16, 780.0), u4, {}, 2);
     CHECK(!fe && flat == std::vector<std::string>({"G0", "G1"}));
     CHECK(alignedAllocFromMatrix(u4, bw, {"G0"}, {}, 2).second.has_value());
+  }
+  // --- config: the reference's own config.yml, byte for byte, plus optional probe keys ---
+  {
+    const char* ref_yml =
+        "# web listen address\nwebListenAddress: \"0.0.0.0:9100\"\n\n# mig strategy\nmigStrategy: \"none\"\n\n"
+        "# enable benchmark\nbenchmark: false\n\n# log configuration\nlog:\n    level: \"debug\"\n    fileDir: \"./logs\"\n";
+    Config c = LoadConfig(ref_yml);
+    CHECK(c.WebListenAddress == "0.0.0.0:9100" && c.MigStrategy == "none" && !c.Benchmark && c.Log.Level == "debug" && c.Log.FileDir == "./logs");
+    CHECK(c.Probe.Enabled && c.Probe.HbmBytes == (16ull << 30) && c.Probe.WoPasses == 64 && c.Probe.IntervalSeconds == 0);
+    Config d = LoadConfig("");
+    CHECK(d.WebListenAddress == "9002" && d.MigStrategy == "none" && d.Log.Level == "debug");  // config.go:16-22
+    Config e3 = LoadConfig(std::string(ref_yml) + "probe:\n  enabled: true\n  hbmBytes: 1073741824   # 1 GiB\n  minCopyGbps: 6000\n  intervalSeconds: 300\n");
+    CHECK(e3.Probe.HbmBytes == (1ull << 30) && e3.Probe.MinCopyGbps == 6000 && e3.Probe.IntervalSeconds == 300 && e3.MigStrategy == "none");
+    gp_config g = e3.ToGpConfig();
+    CHECK(g.struct_size == sizeof(gp_config) && g.hbm_bytes == (1ull << 30) && g.min_copy_gbps == 6000);
   }
   printf("host_selftest ok\n");
   return 0;
