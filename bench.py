@@ -229,20 +229,29 @@ def run_ours(args):
         out = probe.hbm_step(dev, nbytes, w)
         check(out, w)
         triad_sig = (out[2].sum, out[2].xor_, out[2].wsum)
-    probe.kernel_stats(dev, reset=True)
 
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    barrier()
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        out = probe.hbm_step(dev, nbytes, k)   # blocks; 144 B of results come back D2H each step
-        check(out, k)
-        if triad_sig is not None and (out[2].sum, out[2].xor_, out[2].wsum) != triad_sig:
-            raise SystemExit(f"step {k}: triad checksum changed between steps")
-    barrier()
-    wall = time.perf_counter() - t0
-    clocks = sampler.finish()
+    BAD = {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+    attempts = 0
+    while True:
+        attempts += 1
+        probe.kernel_stats(dev, reset=True)
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            out = probe.hbm_step(dev, nbytes, k)   # blocks; 144 B of results come back D2H each step
+            check(out, k)
+            if triad_sig is not None and (out[2].sum, out[2].xor_, out[2].wsum) != triad_sig:
+                raise SystemExit(f"step {k}: triad checksum changed between steps")
+        barrier()
+        wall = time.perf_counter() - t0
+        clocks = sampler.finish()
+        # a run that saw a hardware / thermal slowdown is taken again, once
+        throttled = bool(BAD & set(clocks.get("reasons", [])))
+        if max_over_ranks(dist, [1.0 if throttled else 0.0], "cuda")[0] == 0.0 or attempts >= 2:
+            break
+    clocks["attempts"] = attempts
     stats = probe.kernel_stats(dev)
     dev_ms = stats[gpuprobe.GP_K_STEP].total_ms
 
