@@ -196,7 +196,7 @@ uint32_t gp_abi_version(void);
 /* sizeof() of the POD structs as this library was compiled, so a binding in
  * another language can check its own layout: which = 0 gp_config,
  * 1 gp_pattern_result, 2 gp_timing, 3 gp_gemm_result, 4 gp_device_result,
- * 5 gp_kernel_stat; 0 for anything else. */
+ * 5 gp_kernel_stat, 6 gp_nvml_info; 0 for anything else. */
 size_t gp_sizeof(int which);
 const char* gp_strerror(int err);
 /* Thread-local text of the last failure on this thread ("" if none). */
@@ -205,6 +205,21 @@ const char* gp_last_error_detail(void);
 /* ---- enumeration (mirrors device/device.go:37-43 GetUUID) ---------------- */
 int gp_device_count(gp_ctx* ctx);
 int gp_device_uuid(gp_ctx* ctx, int ordinal, char* buf, size_t buflen);
+
+/* Clocks, power, throttle reasons and — what the plugin gates its periodic re-probe on — how
+ * many OTHER processes are computing on the device right now.  Read through NVML
+ * (dlopen libnvidia-ml.so.1, the library go-nvml binds, reference go.mod:8); when it is not
+ * loadable the call still returns GP_OK with available = 0. */
+typedef struct gp_nvml_info {
+  uint32_t struct_size;
+  uint32_t available;          /* 1 iff NVML answered for this device */
+  uint32_t sm_clock_mhz, sm_clock_max_mhz, mem_clock_mhz;
+  uint32_t power_mw, temperature_c;
+  uint32_t other_compute_procs;/* compute processes on the device, not counting the caller */
+  uint64_t throttle_reasons;   /* nvmlClocksEventReasons bit mask */
+  uint64_t mem_used_bytes, mem_total_bytes;
+} gp_nvml_info;
+int gp_nvml_snapshot(gp_ctx* ctx, const char* uuid, gp_nvml_info* out);
 
 /* ---- the probe: verdict that replaces `dev.Health = pluginapi.Healthy`
  *      (device/devices.go:74); dispatched from the device-map build loop

@@ -446,6 +446,7 @@ size_t gp_sizeof(int which) {
     case 3: return sizeof(gp_gemm_result);
     case 4: return sizeof(gp_device_result);
     case 5: return sizeof(gp_kernel_stat);
+    case 6: return sizeof(gp_nvml_info);
     default: return 0;
   }
 }

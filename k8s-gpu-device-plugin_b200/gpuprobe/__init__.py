@@ -97,6 +97,13 @@ class DeviceResult(C.Structure):
     ]
 
 
+class NvmlInfo(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("available", C.c_uint32), ("sm_clock_mhz", C.c_uint32),
+                ("sm_clock_max_mhz", C.c_uint32), ("mem_clock_mhz", C.c_uint32), ("power_mw", C.c_uint32),
+                ("temperature_c", C.c_uint32), ("other_compute_procs", C.c_uint32),
+                ("throttle_reasons", C.c_uint64), ("mem_used_bytes", C.c_uint64), ("mem_total_bytes", C.c_uint64)]
+
+
 class KernelStat(C.Structure):
     _fields_ = [("launches", C.c_uint64), ("total_ms", C.c_double), ("algo_bytes", C.c_double)]
 
@@ -113,6 +120,7 @@ ABI = [
     ("gp_last_error_detail", C.c_char_p, []),
     ("gp_device_count", C.c_int, [C.c_void_p]),
     ("gp_device_uuid", C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_size_t]),
+    ("gp_nvml_snapshot", C.c_int, [C.c_void_p, C.c_char_p, _P(NvmlInfo)]),
     ("gp_probe_device", C.c_int, [C.c_void_p, C.c_char_p, C.c_uint32, _P(DeviceResult)]),
     ("gp_probe_all", C.c_int, [C.c_void_p, C.c_int, C.c_uint32, _P(DeviceResult), _P(C.c_double)]),
     ("gp_pattern_fill", C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_uint64]),
@@ -222,6 +230,11 @@ class Probe:
 
     def trim(self) -> None:
         self._check(self.lib.gp_trim(self._ctx), "gp_trim")
+
+    def nvml_snapshot(self, uuid) -> NvmlInfo:
+        out = NvmlInfo()
+        self._check(self.lib.gp_nvml_snapshot(self._ctx, _u(uuid), C.byref(out)), "gp_nvml_snapshot")
+        return out
 
     # -- verdicts
     def probe_device(self, uuid, mask: int = GP_PROBE_ALL_SINGLE) -> DeviceResult:

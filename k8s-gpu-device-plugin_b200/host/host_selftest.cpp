@@ -27,8 +27,9 @@ struct FakeInfo : deviceInfo {
 
 // scripted engine: `bad` uuids fail their verdict, `err` uuids make the call itself fail
 struct FakeBackend : ProbeBackend {
-  std::set<std::string> bad, err;
+  std::set<std::string> bad, err, busy;
   int many_calls = 0, slice_calls = 0;
+  int OtherComputeProcs(const std::string& u) override { return busy.count(u) ? 2 : 0; }
   static gp_device_result mk(const std::string& u, bool healthy) {
     gp_device_result r{};
     r.struct_size = sizeof(r);
@@ -187,6 +188,13 @@ int main() {
     std::this_thread::sleep_for(std::chrono::milliseconds(80));
     mgr.StopTicker();
     CHECK(mgr.reprobes() >= before + 3);
+    // the periodic path leaves a busy device alone; the on-demand path does not
+    fb.busy = {"GPU-n0"};
+    const int calls = fb.many_calls;
+    auto [quiet, qe] = mgr.Reprobe("GPU-n0", /*skip_busy=*/true);
+    CHECK(!qe && quiet.empty() && fb.many_calls == calls && mgr.skippedBusy() >= 1);
+    auto [forced, fe2] = mgr.Reprobe("GPU-n0");
+    CHECK(!fe2 && forced.size() == 1 && fb.many_calls == calls + 1);
     PluginManager bad(MigStrategyNone, {Resource::New("GPU", "gpu")}, [&] { return nodes; }, &fb, &pm, 1);
     CHECK(bad.loadPlugins().value() == "GPU name 'NVIDIA B200' does not match any resource patterns");
   }

@@ -201,13 +201,20 @@ class PluginManager {
     return loadPlugins();
   }
   // re-grade (all, or one uuid) while streams are open: transitions go through Report
-  std::pair<std::vector<std::shared_ptr<Device>>, Error> Reprobe(const std::string& uuid = "") {
+  // skip_busy: leave devices alone (keep their last verdict) while other processes compute on them
+  std::pair<std::vector<std::shared_ptr<Device>>, Error> Reprobe(const std::string& uuid = "", bool skip_busy = false) {
     std::lock_guard<std::mutex> g(mu_);
     DeviceMap scope;
+    bool known = false;
     for (auto& kv : devices_.m)
       for (auto& dv : kv.second.m)
-        if (uuid.empty() || dv.second->GetUUID() == uuid) scope.m[kv.first].m[dv.first] = dv.second;
-    if (scope.m.empty()) return {{}, "unknown device " + uuid};
+        if (uuid.empty() || dv.second->GetUUID() == uuid) {
+          known = true;
+          if (skip_busy && be_->OtherComputeProcs(dv.second->GetUUID()) > 0) { ++skipped_busy_; continue; }
+          scope.m[kv.first].m[dv.first] = dv.second;
+        }
+    if (!known) return {{}, "unknown device " + uuid};
+    if (scope.m.empty()) return {{}, std::nullopt};
     GradeDevices(scope, *be_, mask_, &log_, /*apply_health=*/false);
     auto all = scope.All();
     for (auto& d : all) {
@@ -225,7 +232,7 @@ class PluginManager {
       while (ticking_) {
         if (tick_cv_.wait_for(lk, interval, [this] { return !ticking_; })) break;
         lk.unlock();
-        Reprobe("");
+        Reprobe("", /*skip_busy=*/true);
         lk.lock();
       }
     });
@@ -239,6 +246,7 @@ class PluginManager {
   DeviceMap& devices() { return devices_; }
   int loads() const { return loads_; }
   int reprobes() const { return reprobes_; }
+  int skippedBusy() const { return skipped_busy_; }
   int unhealthyAtLoad() const { return unhealthy_at_load_; }
   std::vector<std::string> log() { std::lock_guard<std::mutex> g(mu_); return log_; }
 
@@ -254,7 +262,7 @@ class PluginManager {
   std::vector<std::shared_ptr<NvidiaDevicePlugin>> plugins_;
   std::vector<std::string> log_;
   std::atomic<bool> restart_{false};
-  std::atomic<int> loads_{0}, reprobes_{0};
+  std::atomic<int> loads_{0}, reprobes_{0}, skipped_busy_{0};
   int unhealthy_at_load_ = 0;
   std::thread ticker_;
   std::mutex tick_mu_;

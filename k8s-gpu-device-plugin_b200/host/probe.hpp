@@ -35,6 +35,9 @@ struct ProbeBackend {
   // one MIG slice: must run in its own process (a CUDA process sees one compute instance)
   virtual int ProbeSlice(const std::string& mig_uuid, uint32_t mask, gp_device_result* out,
                          std::string* err) = 0;
+  // compute processes other than ours on the device right now (0 when unknown): a 16 GiB,
+  // full-SM probe perturbs tenants, so the PERIODIC re-probe skips busy devices
+  virtual int OtherComputeProcs(const std::string& /*uuid*/) { return 0; }
 };
 
 class GpuProbeBackend : public ProbeBackend {
@@ -66,6 +69,12 @@ class GpuProbeBackend : public ProbeBackend {
     for (size_t i = 0; i < uuids.size(); ++i)
       if (rcs[i]) { if (err) *err = uuids[i] + ": " + errs[i]; return rcs[i]; }
     return GP_OK;
+  }
+
+  int OtherComputeProcs(const std::string& uuid) override {
+    gp_nvml_info i;
+    if (!ctx_ || gp_nvml_snapshot(ctx_, uuid.c_str(), &i) != GP_OK || !i.available) return 0;
+    return (int)i.other_compute_procs;
   }
 
   // fork + exec the slice binary with CUDA_VISIBLE_DEVICES=<uuid>; it writes the POD result

@@ -77,3 +77,15 @@ def test_two_contexts_coexist():
         b.pattern_fill("0", 2, 1, 4096)
         assert a.pattern_verify("0", 0, 3, 4096).mismatches == 0
         assert b.pattern_verify("0", 2, 1, 4096).mismatches == 0
+
+
+def test_nvml_snapshot():
+    with gpuprobe.Probe() as p:
+        i = p.nvml_snapshot(p.device_uuid(0))
+        if not i.available:
+            pytest.skip("NVML not loadable on this box")
+        assert 100 < i.sm_clock_max_mhz < 4000 and i.sm_clock_mhz <= i.sm_clock_max_mhz
+        assert i.mem_total_bytes > (100 << 30) and i.power_mw > 1000 and 0 < i.temperature_c < 110
+        assert i.other_compute_procs == 0  # a fresh box: nobody else is computing here
+        with pytest.raises(gpuprobe.GpuProbeError):
+            p.nvml_snapshot("GPU-00000000-0000-0000-0000-000000000000")
