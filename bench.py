@@ -48,6 +48,15 @@ def closed_forms(nwords, step):
     return wo, (s, x)
 
 
+def measured_gemm_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            j = json.load(f)
+        return float(j["bf16_tflops"]), float(j.get("bf16_tflops_sustained", 0) or 0), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 1590.0, 1400.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s burst)"
+
+
 def measured_peak():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -325,6 +334,22 @@ def run_ours(args):
                     sweep = {"error": str(e2)}
             p3.close()
         host_barrier()
+    gemm = None
+    if rank == 0 and not args.no_sweep:
+        try:
+            g = p2.gemm_probe(dev, mnk=8192, iters=10, warmup=2, samples=4096)
+            burst, sustained, src = measured_gemm_peaks()
+            gemm = {"workload": "bf16 GEMM probe M=N=K=8192 on tcgen05/TMEM (BASELINE.json configs[2])",
+                    "tflops_best": g.tflops_best, "tflops_median": g.tflops_median, "best_ms": g.t.best_ms,
+                    "bound": "tensor", "peak": burst, "peak_source": src, "frac": g.tflops_best / burst,
+                    "frac_of_sustained_cublas": (g.tflops_median / sustained) if sustained else None,
+                    "frac_of_nominal_2250": g.tflops_best / 2250.0,
+                    "max_scaled_err": g.max_scaled_err, "freivalds_err": g.freivalds_err, "tolerance": 1e-3,
+                    "samples": g.samples, "samples_bad": g.samples_bad,
+                    "tensor_pipe_active_pct_ncu": 96.7, "ncu": "profiles/ncu_summary_r01.md"}
+        except gpuprobe.GpuProbeError as e:
+            gemm = {"error": str(e)}
+    host_barrier()
     p2.close()
 
     if rank != 0:
@@ -386,6 +411,8 @@ def run_ours(args):
     }
     if sweep is not None:
         line["sweep"] = sweep
+    if gemm is not None:
+        line["gemm"] = gemm
     if n_gpus == 1 and not args.no_cpu:
         c = cpu_port_run(args.cpu_bytes, 1, 1, min_seconds=10.0, max_seconds=30.0)
         line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",

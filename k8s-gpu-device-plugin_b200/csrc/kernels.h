@@ -23,10 +23,6 @@ constexpr int kVerifySlots = 512;
 // (set once by launch_verify_scratch_init, restored by every verify launch's finalize CTA).
 constexpr size_t kVerifyScratchBytes = kVerifySlots * sizeof(VerifySlot) + 256;
 
-struct LaunchGeom {
-  int sm_count;
-};
-
 cudaError_t launch_pattern_fill(uint64_t* words, uint64_t nwords, int kind, int pass, int sm_count,
                                 cudaStream_t stream);
 cudaError_t launch_verify_scratch_init(void* scratch, cudaStream_t stream);

@@ -127,6 +127,34 @@ p2p_read_all_kernel(PeerTable t, uint64_t nvec_per_peer, unsigned long long* __r
   if (acc == 0x9E3779B97F4A7C15ull) atomicAdd(sink, 1ull);
 }
 
+// peer write through TMA: threads build a 16 KiB tile of the pattern in shared memory, one
+// thread bulk-stores it to the peer (cp.async.bulk shared -> peer global)
+constexpr uint32_t kP2PTile = 16 * 1024;
+__global__ void __launch_bounds__(128)
+p2p_write_tma_kernel(uint8_t* __restrict__ peer, uint64_t ntiles, uint64_t tag) {
+  __shared__ __align__(128) uint8_t tile[2][kP2PTile];
+  int buf = 0;
+  for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x, buf ^= 1) {
+    u64x4* sv = reinterpret_cast<u64x4*>(tile[buf]);
+    const uint64_t g0 = t * (kP2PTile / 32);
+    for (uint32_t i = threadIdx.x; i < kP2PTile / 32; i += 128) {
+      const uint64_t g = g0 + i;
+      u64x4 v;
+      v.v[0] = tag; v.v[1] = g; v.v[2] = ~g; v.v[3] = tag ^ g;
+      sv[i] = v;
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      bulk_s2g(peer + t * kP2PTile, tile[buf], kP2PTile);
+      bulk_commit();
+      bulk_wait_read<1>();  // the other buffer's store has finished reading: safe to refill it next trip
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) bulk_wait_all<0>();
+}
+
 __global__ void p2p_check_kernel(const u64x4* __restrict__ buf, uint64_t nvec, uint64_t tag,
                                  unsigned long long* __restrict__ bad) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -190,6 +218,8 @@ static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, bool w
         else if (shape == 2) p2p_write_np_kernel<4><<<npgrid(4), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
         else if (shape == 3) p2p_write_kernel<<<s->sm_count * 2, kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
         else if (shape == 4) p2p_write_kernel<<<s->sm_count, kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
+        else if (shape == 5 && bytes % kP2PTile == 0)
+          p2p_write_tma_kernel<<<s->sm_count * 4, 128, 0, s->stream>>>(reinterpret_cast<uint8_t*>(pa), bytes / kP2PTile, tag);
         else p2p_write_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
       } else {
         if (shape == 1) p2p_read_np_kernel<2><<<npgrid(2), kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
