@@ -83,18 +83,28 @@ __device__ __forceinline__ void tma_prefetch_desc(const void* p) {
 }
 template <int CG>
 __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const void* map, uint32_t mbar,
-                                            int c0, int c1) {
+                                            int c0, int c1, uint64_t policy) {
   if constexpr (CG == 1) {
     asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
-            "r"(smem_dst), "l"(map), "r"(mbar), "r"(c0), "r"(c1)
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::
+            "r"(smem_dst), "l"(map), "r"(mbar), "r"(c0), "r"(c1), "l"(policy)
         : "memory");
   } else {
     asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
-            "r"(smem_dst), "l"(map), "r"(mbar), "r"(c0), "r"(c1)
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::
+            "r"(smem_dst), "l"(map), "r"(mbar), "r"(c0), "r"(c1), "l"(policy)
         : "memory");
   }
+}
+__device__ __forceinline__ uint64_t l2_policy(int kind) {  // 0 normal, 1 evict_last, 2 evict_first
+  uint64_t p;
+  if (kind == 1) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  else if (kind == 2) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void st_f4_hint(float* p, float a, float b, float c, float d, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -187,7 +197,7 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
 template <int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 float* __restrict__ C, int M, int N, int K, int group_m) {
+                 float* __restrict__ C, int M, int N, int K, int group_m, int hints) {
   using Cfg = GemmCfg<CG>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle-128B needs 1024-byte alignment
@@ -241,6 +251,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (elect_one()) {
       int stage = 0; uint32_t phase = 0;
       const uint32_t full_leader = CG == 2 ? map_to_cta(full_bar(0), 0) : full_bar(0);
+      const uint64_t pol_a = l2_policy(hints & 3), pol_b = l2_policy((hints >> 2) & 3);
       for (int t = unit; t < num_tiles; t += num_units) {
         int tm, tn;
         tile_coords(t, tm, tn);
@@ -253,8 +264,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           const uint32_t fb = full_leader + 8u * stage;
           if (leader)
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full_bar(stage)), "r"(Cfg::kTxBytes) : "memory");
-          tma_load_2d<CG>(sa, &map_a, fb, kb * kBlockK, row_a);
-          tma_load_2d<CG>(sb, &map_b, fb, kb * kBlockK, row_b);
+          tma_load_2d<CG>(sa, &map_a, fb, kb * kBlockK, row_a, pol_a);
+          tma_load_2d<CG>(sb, &map_b, fb, kb * kBlockK, row_b, pol_b);
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -293,6 +304,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const int quarter = warp & 3;  // a warp may only touch TMEM lanes [32 q, 32 q + 32)
     int acc = 0; uint32_t acc_phase = 0;
     const uint32_t tempty_leader = CG == 2 ? map_to_cta(tempty_bar(0), 0) : tempty_bar(0);
+    const uint64_t pol_c = l2_policy((hints >> 4) & 3);
     for (int t = unit; t < num_tiles; t += num_units) {
       int tm, tn;
       tile_coords(t, tm, tn);
@@ -308,7 +320,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 8; ++q)
-          *reinterpret_cast<float4*>(crow + c * 32 + q * 4) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          st_f4_hint(crow + c * 32 + q * 4, v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3], pol_c);
       }
       tc_fence_before();
       __syncwarp();
@@ -438,7 +450,12 @@ static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, 
   // raster group height in tile rows (development override: GPUPROBE_GEMM_GROUP_M)
   static const int env_group = getenv("GPUPROBE_GEMM_GROUP_M") ? atoi(getenv("GPUPROBE_GEMM_GROUP_M")) : 0;
   const int group_m = env_group > 0 ? env_group : 16 / CG;
-  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, C, M, N, K, group_m);
+  // L2 policies, 2 bits each for A | B << 2 | C << 4 (0 normal, 1 evict_last, 2 evict_first)
+  static const int env_hints = getenv("GPUPROBE_GEMM_HINTS") ? atoi(getenv("GPUPROBE_GEMM_HINTS")) : -1;
+  // measured at 8192^3, 20 launches each: operands evict_last + C evict_first 1462 TFLOP/s median,
+  // no hints 1438; operand panels are re-read by the next wave, C is written once and never read
+  const int hints = env_hints >= 0 ? env_hints : (1 | (1 << 2) | (2 << 4));
+  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, C, M, N, K, group_m, hints);
 }
 
 // function attributes are per device: called once from device_prepare with the device current

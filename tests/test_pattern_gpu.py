@@ -124,6 +124,24 @@ def test_full_size_closed_forms(probe):
     probe.trim()
 
 
+def test_maximum_size_96GiB_indices_past_2_pow_32(probe):
+    """Half the card in one launch: 96 GiB = 1.29e10 words, word indices need 34 bits.  Closed forms
+    (mod 2^64) for sum and xor, no mismatches, and a fault planted above index 2^33 found exactly."""
+    probe.trim()
+    with gpuprobe.Probe(keep_arena=0, arena_cap_bytes=100 << 30) as big:
+        n = (96 << 30) // 8
+        for kind, pas in [(WO, 63), (AD, 0)]:
+            big.pattern_fill(DEV, kind, pas, n)
+            r = big.pattern_verify(DEV, kind, pas, n)
+            s, x = closed_sum_xor(kind, pas, n)
+            assert (r.sum, r.xor_, r.mismatches, r.first_bad_index) == (s, x, 0, M64), (kind, pas)
+        j = (1 << 33) + 987654321
+        big.inject_bitflip(DEV, j, 5)
+        big.inject_bitflip(DEV, n - 1, 63)
+        r = big.pattern_verify(DEV, AD, 0, n)
+        assert (r.mismatches, r.first_bad_index, r.first_bad_xor) == (2, j, 1 << 5)
+
+
 def test_invalid_arguments(probe):
     for args in [(WO, 64, 64), (AD, 2, 64), (7, 0, 64), (WO, 0, 65)]:
         with pytest.raises(gpuprobe.GpuProbeError) as e:
