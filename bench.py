@@ -73,7 +73,7 @@ class ClockSampler(threading.Thread):
                0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
                0x2: "applications_clocks_setting", 0x10: "sync_boost"}
 
-    def __init__(self, index, period=0.05):
+    def __init__(self, index, period=0.05, uuid=None):
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
@@ -83,7 +83,13 @@ class ClockSampler(threading.Thread):
             import pynvml
             pynvml.nvmlInit()
             self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            # CUDA and NVML may enumerate in different orders: address the GPU by UUID when we have it
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode() if isinstance(uuid, str) else uuid) if uuid else None
+            except Exception:
+                self.h = None
+            if self.h is None:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
             self.ok = True
         except Exception as e:  # no NVML: report that, do not invent clocks
@@ -244,7 +250,7 @@ def run_ours(args):
     while True:
         attempts += 1
         probe.kernel_stats(dev, reset=True)
-        sampler = ClockSampler(local_rank)
+        sampler = ClockSampler(local_rank, uuid=dev)
         sampler.start()
         barrier()
         t0 = time.perf_counter()

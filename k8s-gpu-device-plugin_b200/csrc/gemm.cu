@@ -15,7 +15,7 @@
 //   * warp 1: allocates the 512 TMEM columns, and its elected lane issues tcgen05.mma
 //     (kind::f16, bf16 x bf16 -> fp32), releasing stages with tcgen05.commit;
 //   * warps 2-5: epilogue, tcgen05.ld 32 lanes x 32 columns at a time -> registers ->
-//     st.global.v4; two accumulator stages (2 x 256 TMEM columns) so the epilogue of tile t
+//     256-bit st.global (one full L2 sector per lane); two accumulator stages (2 x 256 TMEM columns) so the epilogue of tile t
 //     overlaps the main loop of tile t+1.
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -103,8 +103,11 @@ __device__ __forceinline__ uint64_t l2_policy(int kind) {  // 0 normal, 1 evict_
   else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
   return p;
 }
-__device__ __forceinline__ void st_f4_hint(float* p, float a, float b, float c, float d, uint64_t pol) {
-  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "l"(pol) : "memory");
+// 32 bytes (one full L2 sector) per lane per store: STG.E.256
+__device__ __forceinline__ void st_f8_hint(float* p, const float* v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;" ::"l"(p),
+               "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]), "l"(pol)
+               : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -319,8 +322,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
         tmem_ld_wait();
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          st_f4_hint(crow + c * 32 + q * 4, v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3], pol_c);
+        for (int q = 0; q < 4; ++q) st_f8_hint(crow + c * 32 + q * 8, v + 8 * q, pol_c);
       }
       tc_fence_before();
       __syncwarp();
