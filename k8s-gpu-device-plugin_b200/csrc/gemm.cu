@@ -48,7 +48,8 @@ struct GemmCfg {
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = CG == 2 ? 6 : 4;  // 6 x 32 KiB or 4 x 48 KiB = 192 KiB
   static constexpr uint32_t kTxBytes = kStageBytes * CG;  // bytes landing per stage on the leader's barrier
-  static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr uint32_t kEpiBytes = 2 * 4 * 4096;  // 2 buffers x 4 epilogue warps x (32 rows x 128 B)
+  static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
   static constexpr int kTileM = kBlockM * CG;
 };
 
@@ -200,11 +201,13 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
 template <int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 float* __restrict__ C, int M, int N, int K, int group_m, int hints) {
+                 const __grid_constant__ CUtensorMap map_c, float* __restrict__ C, int M, int N, int K,
+                 int group_m, int hints) {
   using Cfg = GemmCfg<CG>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle-128B needs 1024-byte alignment
-  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  const uint32_t epi_base = smem_base + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned: stage bytes are multiples of 1024
+  const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * Cfg::kStages + a); };
@@ -218,6 +221,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_c);
     for (int s = 0; s < Cfg::kStages; ++s) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(full_bar(s)));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty_bar(s)));
@@ -308,6 +312,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     int acc = 0; uint32_t acc_phase = 0;
     const uint32_t tempty_leader = CG == 2 ? map_to_cta(tempty_bar(0), 0) : tempty_bar(0);
     const uint64_t pol_c = l2_policy((hints >> 4) & 3);
+    uint32_t epi_count = 0;
     for (int t = unit; t < num_tiles; t += num_units) {
       int tm, tn;
       tile_coords(t, tm, tn);
@@ -316,13 +321,47 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const int row = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32 + lane;
       float* crow = C + (size_t)row * N + (size_t)tn * kTileN;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * kTileN);
+      if (hints & 128) {  // development path: direct 256-bit stores from registers
 #pragma unroll 1
-      for (int c = 0; c < kTileN / 32; ++c) {
-        float v[32];
-        tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
-        tmem_ld_wait();
+        for (int c = 0; c < kTileN / 32; ++c) {
+          float v[32];
+          tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
+          tmem_ld_wait();
+          if (!(hints & 64) || v[0] == 123.456f)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) st_f8_hint(crow + c * 32 + q * 8, v + 8 * q, pol_c);
+            for (int q = 0; q < 4; ++q) st_f8_hint(crow + c * 32 + q * 8, v + 8 * q, pol_c);
+        }
+      } else {
+        // registers -> this warp's 32 x 32 fp32 staging tile (128-byte rows, 16-byte chunks XOR-swizzled
+        // by row & 7 exactly as the tensor map's SWIZZLE_128B expects, which also makes the st.shared.v4
+        // conflict-free) -> one TMA store per chunk; two staging buffers per warp
+        const int ewarp = warp - 2;
+        const int tile_row0 = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32;
+#pragma unroll 1
+        for (int c = 0; c < kTileN / 32; ++c) {
+          float v[32];
+          tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
+          const uint32_t buf = epi_base + (uint32_t)(((epi_count & 1) * 4 + ewarp) * 4096);
+          if (lane == 0) bulk_wait_read<1>();  // the store that last used this buffer has read it
+          __syncwarp();
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t addr = buf + (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4));
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v[4 * j]), "f"(v[4 * j + 1]),
+                         "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            asm volatile(
+                "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(&map_c),
+                "r"(buf), "r"(tn * kTileN + c * 32), "r"(tile_row0), "l"(pol_c)
+                : "memory");
+            bulk_commit();
+          }
+          ++epi_count;
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -332,6 +371,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
       if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) bulk_wait_all<0>();  // this warp's TMA stores have completed
   }
 
   tc_fence_before();
@@ -432,8 +472,8 @@ static int gemm_cta_group() {
 }
 
 template <int CG>
-static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, float* C, int M, int N,
-                                  int K, int sm_count, cudaStream_t stream) {
+static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, float* C,
+                                  int M, int N, int K, int sm_count, cudaStream_t stream) {
   using Cfg = GemmCfg<CG>;
   const int tiles = (M / Cfg::kTileM) * (N / kTileN);
   int units = std::min(tiles, sm_count / CG);
@@ -457,7 +497,7 @@ static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, 
   // measured at 8192^3, 20 launches each: operands evict_last + C evict_first 1462 TFLOP/s median,
   // no hints 1438; operand panels are re-read by the next wave, C is written once and never read
   const int hints = env_hints >= 0 ? env_hints : (1 | (1 << 2) | (2 << 4));
-  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, C, M, N, K, group_m, hints);
+  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, mc, C, M, N, K, group_m, hints);
 }
 
 // function attributes are per device: called once from device_prepare with the device current
@@ -471,10 +511,25 @@ cudaError_t gemm_kernels_configure() {
 
 struct GemmPlan {
   int cg;
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, mc;
 };
 
-static int make_plan(GemmPlan* p, const void* A, const void* B, uint32_t m, uint32_t n, uint32_t k) {
+// C (fp32, row-major M x N) as a 2-D map with a 32 x 32 box (128-byte rows) and 128-byte swizzle
+static int make_map_c(CUtensorMap* map, const void* base, uint64_t M, uint64_t N) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return GP_ERR_UNSUPPORTED; }
+  const cuuint64_t dims[2] = {N, M};
+  const cuuint64_t strides[1] = {N * 4};
+  const cuuint32_t box[2] = {32, 32};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (C) failed: %d", (int)r); return GP_ERR_CUDA; }
+  return GP_OK;
+}
+
+static int make_plan(GemmPlan* p, const void* A, const void* B, const void* C, uint32_t m, uint32_t n, uint32_t k) {
   p->cg = gemm_cta_group();
   if (m % 256 || n % 256 || k % 64 || m == 0 || n == 0 || k == 0) {
     set_error("gemm needs m, n multiples of 256 and k a multiple of 64");
@@ -482,13 +537,15 @@ static int make_plan(GemmPlan* p, const void* A, const void* B, uint32_t m, uint
   }
   int rc = make_map(&p->ma, A, m, k, kBlockM);
   if (rc) return rc;
+  rc = make_map_c(&p->mc, C, m, n);
+  if (rc) return rc;
   return make_map(&p->mb, B, n, k, (uint32_t)(kTileN / p->cg));
 }
 
 static cudaError_t launch_gemm(const GemmPlan& p, float* C, int M, int N, int K, int sm_count,
                                cudaStream_t stream) {
-  return p.cg == 2 ? launch_gemm_cg<2>(p.ma, p.mb, C, M, N, K, sm_count, stream)
-                   : launch_gemm_cg<1>(p.ma, p.mb, C, M, N, K, sm_count, stream);
+  return p.cg == 2 ? launch_gemm_cg<2>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
+                   : launch_gemm_cg<1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
 }
 
 #define CU_OR_RETURN(call)                                               \
@@ -518,7 +575,7 @@ int gemm_host_locked(Ctx* ctx, Device* d, const uint16_t* a, const uint16_t* b, 
   uint8_t* B = A + up(a_bytes);
   float* C = reinterpret_cast<float*>(B + up(b_bytes));
   GemmPlan plan;
-  rc = make_plan(&plan, A, B, m, n, k);
+  rc = make_plan(&plan, A, B, C, m, n, k);
   if (rc) return rc;
   CU_OR_RETURN(cudaMemcpyAsync(A, a, a_bytes, cudaMemcpyHostToDevice, d->stream));
   CU_OR_RETURN(cudaMemcpyAsync(B, b, b_bytes, cudaMemcpyHostToDevice, d->stream));
@@ -561,7 +618,7 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   float* d_sampled = reinterpret_cast<float*>(p);
 
   GemmPlan plan;
-  rc = make_plan(&plan, A, B, m, n, k);
+  rc = make_plan(&plan, A, B, C, m, n, k);
   if (rc) return rc;
   cudaStream_t s = d->stream;
   CU_OR_RETURN(launch_gen_bf16(A, (uint64_t)m * k, seed, d->sm_count, s));
