@@ -102,3 +102,17 @@ def test_gemm_invalid_shapes(probe):
         with pytest.raises(gpuprobe.GpuProbeError) as e:
             probe.gemm_host(DEV, z, z, c, m, n, k)
         assert e.value.code == gpuprobe.GP_ERR_INVALID
+
+
+def test_gemm_golden_points(probe, oracle, cta_group):
+    """The generated problem at the committed fixture positions (tests/golden/stream_gemm_golden.json)."""
+    import json
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "stream_gemm_golden.json")))
+    for g in gold["gemm"]:
+        n = g["mnk"]
+        a = oracle_lib.gen_bf16(oracle, g["seed"], 0, n * n)
+        b = oracle_lib.gen_bf16(oracle, g["seed"] ^ oracle_lib.SEED_B_XOR, 0, n * n)
+        c = np.zeros((n, n), dtype=np.float32)
+        probe.gemm_host(DEV, a, b, c, n, n, n)
+        for pt in g["points"]:
+            assert abs(float(c[pt["i"], pt["j"]]) - pt["ref"]) <= TOL * pt["absdot"], pt

@@ -210,3 +210,18 @@ def test_cpu_hbm_step_is_consistent(oracle):
     assert (out[2].sum, out[2].xor_, out[2].wsum, out[2].mismatches) == (chk.sum, chk.xor_, chk.wsum, 0)
     z = arena[2 * nbytes:3 * nbytes].view(np.float32)
     assert np.array_equal(z, ref)
+
+
+def test_golden_stream_gemm_fixtures(oracle):
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "stream_gemm_golden.json")))
+    for t in gold["triad"]:
+        n = t["nbytes"] // 4
+        a = np.empty(n, dtype=np.float32)
+        oracle.gp_cpu_triad_gen(a.ctypes.data, t["seed"], t["scalar"], 0, n)
+        r = oracle_lib.verify(oracle, a.view(np.uint64), WO, 0)
+        assert (hex(r.sum), hex(r.xor_), hex(r.wsum)) == (t["sum"], t["xor"], t["wsum"])
+    for g in gold["gemm"]:
+        for pt in g["points"]:
+            ad = C.c_double()
+            v = oracle.gp_cpu_gemm_sample(g["seed"], g["mnk"], pt["i"], pt["j"], C.byref(ad))
+            assert v == pt["ref"] and ad.value == pt["absdot"]

@@ -108,3 +108,11 @@ def test_probe_device_verdict(oracle):
     with gpuprobe.Probe(hbm_bytes=64 << 20, iters=2, warmup=1, min_copy_gbps=1e9) as p:
         r = p.probe_device("0", gpuprobe.GP_PROBE_COPY)
         assert r.healthy == 0 and r.failed_mask == gpuprobe.GP_PROBE_COPY and r.error == 0
+
+
+def test_triad_golden_fixture_on_gpu(probe):
+    import json, os
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "stream_gemm_golden.json")))
+    for t in gold["triad"]:
+        out = probe.hbm_step(DEV, t["nbytes"], step=0)
+        assert (hex(out[2].sum), hex(out[2].xor_), hex(out[2].wsum)) == (t["sum"], t["xor"], t["wsum"])
