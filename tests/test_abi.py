@@ -79,3 +79,28 @@ def test_product_does_not_reference_oracle():
                 assert "libgpuprobe_oracle" not in txt and "oracle_lib" not in txt, f
     out = subprocess.run(["ldd", gpuprobe.LIB_PATH], capture_output=True, text=True).stdout
     assert "oracle" not in out
+
+
+def _build_c_driver(tmp_path):
+    exe = str(tmp_path / "c_abi_driver")
+    pkg = os.path.join(ROOT, "k8s-gpu-device-plugin_b200")
+    subprocess.check_call(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "c_abi_driver.c"), "-o", exe, "-L", pkg, "-lgpuprobe",
+                           "-Wl,-rpath," + pkg])
+    return exe
+
+
+@pytest.mark.skipif(_has_gpu(), reason="CPU variant; the GPU variant is test_c_driver_on_gpu")
+def test_header_is_valid_c99_and_driver_fails_loudly_without_gpu(tmp_path):
+    """cgo compiles the header as C: it must be valid C99, and a C caller must see the same
+    struct sizes as the library."""
+    r = subprocess.run([_build_c_driver(tmp_path)], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 3, (r.returncode, r.stdout, r.stderr)
+    assert "no GPU: gp_init" in r.stdout
+
+
+@pytest.mark.gpu
+def test_c_driver_on_gpu(tmp_path):
+    r = subprocess.run([_build_c_driver(tmp_path)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "c_abi_driver ok" in r.stdout
