@@ -215,6 +215,15 @@ int main() {
     auto [flat, fe] = alignedAllocFromMatrix(u4, std::vector<double>(16, 780.0), u4, {}, 2);
     CHECK(!fe && flat == std::vector<std::string>({"G0", "G1"}));
     CHECK(alignedAllocFromMatrix(u4, bw, {"G0"}, {}, 2).second.has_value());
+    // getPreferredAllocation picks the branch as plugin.go:248-254 does
+    Devices whole;
+    for (const auto& u : u4) { auto d = std::make_shared<Device>(); d->ID = u; d->Index = u.substr(1); d->Paths = {"/dev/nvidia" + u.substr(1)}; whole.m[u] = d; }
+    auto [p1, pe1] = getPreferredAllocation(whole, P2PMatrix{u4, bw}, u4, {"G1"}, 2);
+    CHECK(!pe1 && p1[0] == "G1" && p1[1] != "G0");                 // steers around the degraded 0<->1 link
+    auto [p2, pe2] = getPreferredAllocation(whole, P2PMatrix{}, {"G3", "G2"}, {}, 1);
+    CHECK(!pe2 && p2 == std::vector<std::string>({"G2"}));         // no matrix yet: id order
+    auto [p3, pe3] = getPreferredAllocation(reps, P2PMatrix{u4, bw}, {"GPU-a::0", "GPU-a::1", "GPU-b::0", "GPU-b::1"}, {}, 2);
+    CHECK(!pe3 && AnnotatedID{p3[0]}.GetID() != AnnotatedID{p3[1]}.GetID());  // annotated ids -> distributedAlloc
   }
   // --- config: the reference's own config.yml, byte for byte, plus optional probe keys ---
   {

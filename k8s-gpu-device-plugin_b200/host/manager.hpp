@@ -167,6 +167,32 @@ inline std::pair<std::vector<std::string>, Error> alignedAllocFromMatrix(
   return {chosen, std::nullopt};
 }
 
+// plugin/plugin.go:192-207,248-254: GetPreferredAllocation -> getPreferredAllocation.  Aligned
+// allocation when every device supports it and no id is annotated (a replica), else spread over
+// replicas.  The aligned branch ranks by the measured P2P matrix instead of go-gpuallocator's NVML
+// link query; with no matrix measured yet it degrades to id order (a flat matrix).
+struct P2PMatrix {
+  std::vector<std::string> uuidByOrdinal;
+  std::vector<double> gbps;  // n*n, row = src
+};
+inline std::pair<std::vector<std::string>, Error> getPreferredAllocation(const Devices& devices, const P2PMatrix& mx,
+                                                                         const std::vector<std::string>& available,
+                                                                         const std::vector<std::string>& mustInclude, int size) {
+  bool annotated = false;
+  for (const auto& a : available) annotated = annotated || AnnotatedID{a}.HasAnnotations();
+  if (devices.AlignedAllocationSupported() && !annotated) {
+    if (mx.uuidByOrdinal.empty()) {
+      P2PMatrix flat;
+      flat.uuidByOrdinal = available;
+      std::sort(flat.uuidByOrdinal.begin(), flat.uuidByOrdinal.end());
+      flat.gbps.assign(flat.uuidByOrdinal.size() * flat.uuidByOrdinal.size(), 1.0);
+      return alignedAllocFromMatrix(flat.uuidByOrdinal, flat.gbps, available, mustInclude, size);
+    }
+    return alignedAllocFromMatrix(mx.uuidByOrdinal, mx.gbps, available, mustInclude, size);
+  }
+  return distributedAlloc(devices, available, mustInclude, size);
+}
+
 // plugin/manager.go:20-194 without the sockets: owns the device map and one plugin per resource.
 class PluginManager {
  public:
