@@ -82,10 +82,19 @@ int resolve_variant(const Ctx* ctx) {
   return GP_STREAM_TMA;  // AUTO: see DESIGN.md "Stream kernels" for the measured choice
 }
 
-int device_prepare(Ctx* ctx, Device* d) {
-  (void)ctx;
-  CU_OR_RETURN(cudaSetDevice(d->ordinal), nullptr);
-  if (d->ready) return GP_OK;
+static void device_release(Device* d) {
+  if (d->scratch) cudaFree(d->scratch);
+  if (d->h_results) cudaFreeHost(d->h_results);
+  for (auto& ev : d->events)
+    if (ev) { cudaEventDestroy(ev); ev = nullptr; }
+  if (d->stream) cudaStreamDestroy(d->stream);
+  d->scratch = nullptr;
+  d->h_results = nullptr;
+  d->stream = nullptr;
+  d->ready = false;
+}
+
+static int device_prepare_once(Device* d) {
   CU_OR_RETURN(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking), nullptr);
   const size_t scratch_bytes =
       kVerifyScratchBytes + kMaxResults * sizeof(gp_pattern_result) + 256;
@@ -101,6 +110,18 @@ int device_prepare(Ctx* ctx, Device* d) {
   CU_OR_RETURN(stream_kernels_configure(), nullptr);
   if (d->cc_major == 10) CU_OR_RETURN(gemm_kernels_configure(), nullptr);
   CU_OR_RETURN(cudaStreamSynchronize(d->stream), nullptr);
+  return GP_OK;
+}
+
+int device_prepare(Ctx* ctx, Device* d) {
+  (void)ctx;
+  CU_OR_RETURN(cudaSetDevice(d->ordinal), nullptr);
+  if (d->ready) return GP_OK;
+  const int rc = device_prepare_once(d);
+  if (rc != GP_OK) {  // nothing half-built survives a failed set-up
+    device_release(d);
+    return rc;
+  }
   d->ready = true;
   return GP_OK;
 }
@@ -515,12 +536,7 @@ void gp_shutdown(gp_ctx* ctx) {
     cudaSetDevice(d->ordinal);
     if (d->stream) cudaStreamSynchronize(d->stream);
     free_arena(d.get());
-    if (d->scratch) cudaFree(d->scratch);
-    if (d->h_results) cudaFreeHost(d->h_results);
-    for (auto& ev : d->events)
-      if (ev) cudaEventDestroy(ev);
-    if (d->stream) cudaStreamDestroy(d->stream);
-    d->ready = false;
+    device_release(d.get());
   }
   delete ctx;
 }
