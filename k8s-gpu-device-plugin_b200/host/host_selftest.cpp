@@ -49,8 +49,10 @@ struct FakeBackend : ProbeBackend {
     }
     return rc;
   }
-  int ProbeSlice(const std::string& u, uint32_t, gp_device_result* out, std::string*) override {
+  uint64_t last_slice_mem = 0;
+  int ProbeSlice(const std::string& u, uint32_t, uint64_t total_mem, gp_device_result* out, std::string*) override {
     ++slice_calls;
+    last_slice_mem = total_mem;
     *out = mk(u, !bad.count(u));
     return 0;
   }
@@ -83,6 +85,9 @@ int main() {
   std::vector<std::string> log;
   CHECK(GradeDevices(dm, be, GP_PROBE_ALL_SINGLE, &log) == 3);
   CHECK(be.many_calls == 1 && be.slice_calls == 2 && log.size() == 3);
+  CHECK(be.last_slice_mem == (180ull << 30));  // the slice's TotalMemory reaches the backend
+  CHECK(GpuProbeBackend::SliceBytes(0, 23ull << 30) == ((23ull << 30) / 4 & ~((1ull << 20) - 1)));  // 1g.23gb: 5.75 GiB arrays
+  CHECK(GpuProbeBackend::SliceBytes(1ull << 30, 180ull << 30) == (1ull << 30) && GpuProbeBackend::SliceBytes(0, 0) == (16ull << 30));
   auto& gpus = dm.m["nvidia.com/gpu"];
   CHECK(gpus.GetByID("GPU-0")->Health == std::string(Healthy) && gpus.GetByID("GPU-1")->Health == std::string(Unhealthy));
   CHECK(gpus.GetByID("GPU-2")->Health == std::string(Unhealthy) && gpus.GetByID("GPU-2")->Probe->error == GP_ERR_CUDA);

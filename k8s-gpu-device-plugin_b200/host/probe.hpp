@@ -11,6 +11,7 @@
 #include <sys/wait.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -33,7 +34,8 @@ struct ProbeBackend {
   virtual int ProbeMany(const std::vector<std::string>& uuids, uint32_t mask,
                         std::vector<gp_device_result>* out, std::string* err) = 0;
   // one MIG slice: must run in its own process (a CUDA process sees one compute instance)
-  virtual int ProbeSlice(const std::string& mig_uuid, uint32_t mask, gp_device_result* out,
+  // total_mem is the slice's memory (device/device.go:175-181): the probe is sized to it
+  virtual int ProbeSlice(const std::string& mig_uuid, uint32_t mask, uint64_t total_mem, gp_device_result* out,
                          std::string* err) = 0;
   // compute processes other than ours on the device right now (0 when unknown): a 16 GiB,
   // full-SM probe perturbs tenants, so the PERIODIC re-probe skips busy devices
@@ -79,7 +81,16 @@ class GpuProbeBackend : public ProbeBackend {
 
   // fork + exec the slice binary with CUDA_VISIBLE_DEVICES=<uuid>; it writes the POD result
   // struct to its stdout.
-  int ProbeSlice(const std::string& uuid, uint32_t mask, gp_device_result* out, std::string* err) override {
+  // arrays of a slice probe: the configured size, but never more than a quarter of the slice
+  // (triad needs three arrays), rounded down to 1 MiB
+  static uint64_t SliceBytes(uint64_t configured, uint64_t total_mem) {
+    uint64_t want = configured ? configured : (16ull << 30);
+    if (total_mem) want = std::min<uint64_t>(want, total_mem / 4);
+    want &= ~((1ull << 20) - 1);
+    return std::max<uint64_t>(want, 1ull << 20);
+  }
+
+  int ProbeSlice(const std::string& uuid, uint32_t mask, uint64_t total_mem, gp_device_result* out, std::string* err) override {
     if (child_.empty()) { if (err) *err = "no slice binary configured"; return GP_ERR_UNSUPPORTED; }
     int fds[2];
     if (pipe(fds) != 0) { if (err) *err = "pipe failed"; return GP_ERR_INVALID; }
@@ -90,8 +101,10 @@ class GpuProbeBackend : public ProbeBackend {
       close(fds[0]);
       close(fds[1]);
       setenv("CUDA_VISIBLE_DEVICES", uuid.c_str(), 1);
-      const std::string m = std::to_string(mask), hb = std::to_string(cfg_.hbm_bytes),
-                        pb = std::to_string(cfg_.pattern_bytes), wo = std::to_string(cfg_.wo_passes),
+      const uint64_t hbm = SliceBytes(cfg_.hbm_bytes, total_mem);
+      const uint64_t pat = std::min<uint64_t>(cfg_.pattern_bytes ? cfg_.pattern_bytes : hbm, hbm);
+      const std::string m = std::to_string(mask), hb = std::to_string(hbm),
+                        pb = std::to_string(pat), wo = std::to_string(cfg_.wo_passes),
                         gm = std::to_string(cfg_.gemm_mnk);
       execl(child_.c_str(), child_.c_str(), m.c_str(), hb.c_str(), pb.c_str(), wo.c_str(), gm.c_str(), (char*)nullptr);
       _exit(127);
@@ -146,7 +159,7 @@ inline int GradeDevices(DeviceMap& dm, ProbeBackend& be, uint32_t mask, std::vec
   std::vector<int> src(slices.size(), 0);
   std::vector<std::string> serr(slices.size());
   for (size_t i = 0; i < slices.size(); ++i)
-    th.emplace_back([&, i] { src[i] = be.ProbeSlice(slices[i]->GetUUID(), mask & ~0u, &sres[i], &serr[i]); });
+    th.emplace_back([&, i] { src[i] = be.ProbeSlice(slices[i]->GetUUID(), mask, slices[i]->TotalMemory, &sres[i], &serr[i]); });
   if (!gpus.empty()) rc = be.ProbeMany(uuids, mask, &res, &err);
   for (auto& t : th) t.join();
   int unhealthy = 0;
