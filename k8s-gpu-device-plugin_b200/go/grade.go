@@ -4,7 +4,6 @@
 package device
 
 import (
-	"strings"
 	"sync"
 
 	bmk "github.com/uppercaveman/k8s-gpu-device-plugin/benchmark"
@@ -86,5 +85,3 @@ func (e HealthEvent) Health() string {
 	}
 	return pluginapi.Unhealthy
 }
-
-var _ = strings.Contains
