@@ -74,6 +74,24 @@ def test_bitflip_fault_injection(probe, oracle, kind, pas):
     assert probe.pattern_verify(DEV, kind, pas, n).astuple() == as_tuple(r)  # idempotent
 
 
+def test_random_single_faults_are_always_found_exactly(probe):
+    """Property: one flipped bit anywhere in 1 GiB, any pattern, any pass, is reported with its
+    exact word index and xor, and sum/xor move by exactly that bit."""
+    rng = np.random.default_rng(2026)
+    n = (1 << 30) // 8
+    for _ in range(24):
+        kind = int(rng.choice([WO, WZ, AD]))
+        pas = int(rng.integers(0, 2 if kind == AD else 64))
+        j = int(rng.integers(0, n))
+        b = int(rng.integers(0, 64))
+        probe.pattern_fill(DEV, kind, pas, n)
+        s, x = closed_sum_xor(kind, pas, n)
+        probe.inject_bitflip(DEV, j, b)
+        r = probe.pattern_verify(DEV, kind, pas, n)
+        assert (r.mismatches, r.first_bad_index, r.first_bad_xor) == (1, j, 1 << b), (kind, pas, j, b)
+        assert r.xor_ == x ^ (1 << b) and (r.sum - s) & M64 in ((1 << b), (-(1 << b)) & M64)
+
+
 def test_wrong_pass_is_all_mismatch(probe, oracle):
     n = 1 << 16
     probe.pattern_fill(DEV, WO, 0, n)
