@@ -309,6 +309,36 @@ def run_ours(args):
                        "The probe takes no bulk host input by construction (patterns are generated "
                        "on the device it grades), so h2d is 0 and d2h is the result bytes."}
 
+    # ---- the literal host-buffer reading of e2e, for the record: grade 1 GiB that lives in pinned HOST
+    # memory (H2D copy + verify + 48-byte result back).  This measures PCIe, not the device, and is not
+    # what the probe is for — the probe grades device memory with patterns generated on the device.
+    e2e_host = None
+    if not args.no_e2e:
+        try:
+            import numpy as np
+            hb_words = (1 << 30) // 8
+            pinned = torch.empty(hb_words, dtype=torch.int64).pin_memory()
+            host_np = pinned.numpy().view(np.uint64)
+            idx = np.arange(hb_words, dtype=np.uint64)
+            host_np[:] = np.left_shift(np.uint64(1), (idx + np.uint64(7)) & np.uint64(63))
+            del idx
+            p2.pattern_host(dev, host_np, gpuprobe.GP_PAT_WALKING_ONES, 7, fill=False)  # warm-up, arena alloc
+            times = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                r = p2.pattern_host(dev, host_np, gpuprobe.GP_PAT_WALKING_ONES, 7, fill=False)
+                times.append(time.perf_counter() - t0)
+                if r.mismatches:
+                    raise SystemExit("host-buffer verify found mismatches")
+            best = min(times)
+            e2e_host = {"value": (1 << 30) / best / 1e9, "unit": UNIT, "h2d_bytes_per_step": 1 << 30,
+                        "d2h_bytes_per_step": 48, "seconds_per_call": best,
+                        "what": "gp_pattern_host(fill=0): verify of a 1 GiB pinned HOST buffer through the C ABI; "
+                                "PCIe-bound by construction, reported for completeness, not the product path"}
+            p2.trim()
+        except gpuprobe.GpuProbeError as e:
+            e2e_host = {"error": str(e)}
+
     # ---- full-box sweep seconds (second half of the metric), rank 0, all N GPUs, one process --
     sweep = None
     if not args.no_sweep:
@@ -419,6 +449,8 @@ def run_ours(args):
         line["sweep"] = sweep
     if gemm is not None:
         line["gemm"] = gemm
+    if e2e_host is not None:
+        line["e2e_host_buffer"] = e2e_host
     if n_gpus == 1 and not args.no_cpu:
         c = cpu_port_run(args.cpu_bytes, 1, 1, min_seconds=10.0, max_seconds=30.0)
         line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
