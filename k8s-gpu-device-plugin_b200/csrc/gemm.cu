@@ -37,20 +37,27 @@ constexpr int kBlockM = 128;  // rows of A (and of the accumulator) per CTA
 constexpr int kBlockK = 64;   // 64 bf16 = 128 bytes = one swizzle span
 constexpr int kUmmaK = 16;    // K per tcgen05.mma for 16-bit inputs
 constexpr int kTileN = 256;   // accumulator columns per tile (UMMA N)
-constexpr int kAccStages = 2; // 2 x 256 = all 512 TMEM columns
 constexpr int kGemmThreads = 192;
 
-template <int CG>
+// CG = CTAs per MMA (tcgen05 cta_group), NT = 256-wide N sub-tiles accumulated per tile.
+// NT = 2 keeps BOTH 256-column TMEM accumulators busy with one 256 x 512 tile that shares every
+// A stage between two MMAs, so a stage moves A + 2B for twice the flops: 25 % fewer operand
+// bytes per flop from L2 (the measured bottleneck) at the price of an
+// epilogue that no longer overlaps the main loop.
+template <int CG, int NT>
 struct GemmCfg {
-  static constexpr int kLoadN = kTileN / CG;  // rows of B staged by each CTA
+  static_assert(NT == 1 || (NT == 2 && CG == 2), "two N sub-tiles need the 2-CTA stage budget");
+  static constexpr int kLoadN = kTileN / CG;  // rows of each B sub-tile staged by each CTA
   static constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
   static constexpr uint32_t kBBytes = kLoadN * kBlockK * 2;
-  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = CG == 2 ? 6 : 4;  // 6 x 32 KiB or 4 x 48 KiB = 192 KiB
+  static constexpr uint32_t kStageBytes = kABytes + NT * kBBytes;
+  static constexpr int kStages = (192 * 1024) / kStageBytes;  // 6 x 32 KiB, 4 x 48 KiB
   static constexpr uint32_t kTxBytes = kStageBytes * CG;  // bytes landing per stage on the leader's barrier
   static constexpr uint32_t kEpiBytes = 2 * 4 * 4096;  // 2 buffers x 4 epilogue warps x (32 rows x 128 B)
   static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
   static constexpr int kTileM = kBlockM * CG;
+  static constexpr int kTileNAll = kTileN * NT;   // output columns per tile
+  static constexpr int kAccStages = 2 / NT;       // TMEM: 512 columns = kAccStages x kTileNAll
 };
 
 // ------------------------------------------------------------ PTX helpers ---
@@ -198,12 +205,13 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
 }
 
 // ---------------------------------------------------------------- kernel ---
-template <int CG>
+template <int CG, int NT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_c, float* __restrict__ C, int M, int N, int K,
                  int group_m, int hints) {
-  using Cfg = GemmCfg<CG>;
+  using Cfg = GemmCfg<CG, NT>;
+  constexpr int kAccStages = Cfg::kAccStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle-128B needs 1024-byte alignment
   const uint32_t epi_base = smem_base + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned: stage bytes are multiples of 1024
@@ -239,7 +247,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  const int tiles_m = M / Cfg::kTileM, tiles_n = N / kTileN;
+  const int tiles_m = M / Cfg::kTileM, tiles_n = N / Cfg::kTileNAll;
   const int num_tiles = tiles_m * tiles_n;
   const int num_kb = K / kBlockK;
   const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
@@ -263,16 +271,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         int tm, tn;
         tile_coords(t, tm, tn);
         const int row_a = tm * Cfg::kTileM + (int)cta_rank * kBlockM;
-        const int row_b = tn * kTileN + (int)cta_rank * Cfg::kLoadN;
+        const int row_b = tn * Cfg::kTileNAll + (int)cta_rank * Cfg::kLoadN;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait_addr(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
           const uint32_t sb = sa + Cfg::kABytes;
           const uint32_t fb = full_leader + 8u * stage;
           if (leader)
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full_bar(stage)), "r"(Cfg::kTxBytes) : "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full_bar(stage)),
+                         "r"(Cfg::kTxBytes) : "memory");
           tma_load_2d<CG>(sa, &map_a, fb, kb * kBlockK, row_a, pol_a);
-          tma_load_2d<CG>(sb, &map_b, fb, kb * kBlockK, row_b, pol_b);
+#pragma unroll
+          for (int nt = 0; nt < NT; ++nt)
+            tma_load_2d<CG>(sb + nt * Cfg::kBBytes, &map_b, fb, kb * kBlockK, row_b + nt * kTileN, pol_b);
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -286,18 +297,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       for (int t = unit; t < num_tiles; t += num_units) {
         mbar_wait_addr(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kTileN);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::kTileNAll);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait_addr(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
           const uint64_t adesc = make_smem_desc(sa);
-          const uint64_t bdesc = make_smem_desc(sa + Cfg::kABytes);
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            // +32 bytes per K step of 16 bf16 -> +2 in the 16-byte-unit address field
-            umma_f16<CG>(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                         (uint32_t)((kb | k) != 0));
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+              // +32 bytes per K step of 16 bf16 -> +2 in the 16-byte-unit address field
+              const uint64_t bdesc = make_smem_desc(sa + Cfg::kABytes + nt * Cfg::kBBytes);
+              umma_f16<CG>(d_tmem + (uint32_t)(nt * kTileN), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k),
+                           idesc, (uint32_t)((kb | k) != 0));
+            }
           }
           umma_commit<CG>(empty_bar(stage));  // frees the stage once these MMAs have read it
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -319,11 +333,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       mbar_wait_addr(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const int row = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32 + lane;
-      float* crow = C + (size_t)row * N + (size_t)tn * kTileN;
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * kTileN);
+      float* crow = C + (size_t)row * N + (size_t)tn * Cfg::kTileNAll;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * Cfg::kTileNAll);
       if (hints & 128) {  // development path: direct 256-bit stores from registers
 #pragma unroll 1
-        for (int c = 0; c < kTileN / 32; ++c) {
+        for (int c = 0; c < Cfg::kTileNAll / 32; ++c) {
           float v[32];
           tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
           tmem_ld_wait();
@@ -338,7 +352,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int ewarp = warp - 2;
         const int tile_row0 = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32;
 #pragma unroll 1
-        for (int c = 0; c < kTileN / 32; ++c) {
+        for (int c = 0; c < Cfg::kTileNAll / 32; ++c) {
           float v[32];
           tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
           const uint32_t buf = epi_base + (uint32_t)(((epi_count & 1) * 4 + ewarp) * 4096);
@@ -356,7 +370,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           if (lane == 0) {
             asm volatile(
                 "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(&map_c),
-                "r"(buf), "r"(tn * kTileN + c * 32), "r"(tile_row0), "l"(pol_c)
+                "r"(buf), "r"(tn * Cfg::kTileNAll + c * 32), "r"(tile_row0), "l"(pol_c)
                 : "memory");
             bulk_commit();
           }
@@ -471,11 +485,11 @@ static int gemm_cta_group() {
   return 2;
 }
 
-template <int CG>
+template <int CG, int NT>
 static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, float* C,
                                   int M, int N, int K, int sm_count, cudaStream_t stream) {
-  using Cfg = GemmCfg<CG>;
-  const int tiles = (M / Cfg::kTileM) * (N / kTileN);
+  using Cfg = GemmCfg<CG, NT>;
+  const int tiles = (M / Cfg::kTileM) * (N / Cfg::kTileNAll);
   int units = std::min(tiles, sm_count / CG);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(units * CG));
@@ -491,26 +505,30 @@ static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, 
   cfg.numAttrs = 1;
   // raster group height in tile rows (development override: GPUPROBE_GEMM_GROUP_M)
   static const int env_group = getenv("GPUPROBE_GEMM_GROUP_M") ? atoi(getenv("GPUPROBE_GEMM_GROUP_M")) : 0;
-  const int group_m = env_group > 0 ? env_group : 16 / CG;
+  // measured at 8192^3: 256x256 tiles 4: 1430, 8: 1475, 16: 1458; 256x512 tiles 4: 1493, 8: 1529, 16: 1540, 32: 1519
+  const int group_m = env_group > 0 ? env_group : (NT == 2 ? 16 : 16 / CG);
   // L2 policies, 2 bits each for A | B << 2 | C << 4 (0 normal, 1 evict_last, 2 evict_first)
   static const int env_hints = getenv("GPUPROBE_GEMM_HINTS") ? atoi(getenv("GPUPROBE_GEMM_HINTS")) : -1;
   // measured at 8192^3, 20 launches each: operands evict_last + C evict_first 1462 TFLOP/s median,
   // no hints 1438; operand panels are re-read by the next wave, C is written once and never read
   const int hints = env_hints >= 0 ? env_hints : (1 | (1 << 2) | (2 << 4));
-  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG>, ma, mb, mc, C, M, N, K, group_m, hints);
+  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG, NT>, ma, mb, mc, C, M, N, K, group_m, hints);
 }
 
 // function attributes are per device: called once from device_prepare with the device current
 cudaError_t gemm_kernels_configure() {
-  cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)GemmCfg<1>::kSmemBytes);
+  cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)GemmCfg<1, 1>::kSmemBytes);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(gemm_bf16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)GemmCfg<2>::kSmemBytes);
+  e = cudaFuncSetAttribute(gemm_bf16_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)GemmCfg<2, 1>::kSmemBytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(gemm_bf16_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)GemmCfg<2, 2>::kSmemBytes);
 }
 
 struct GemmPlan {
-  int cg;
+  int cg, nt;
   CUtensorMap ma, mb, mc;
 };
 
@@ -531,6 +549,9 @@ static int make_map_c(CUtensorMap* map, const void* base, uint64_t M, uint64_t N
 
 static int make_plan(GemmPlan* p, const void* A, const void* B, const void* C, uint32_t m, uint32_t n, uint32_t k) {
   p->cg = gemm_cta_group();
+  // 256 x 512 tiles (two N sub-tiles per CTA pair) whenever the shape allows; GPUPROBE_GEMM_NT=1 forces 256 x 256
+  static const int env_nt = getenv("GPUPROBE_GEMM_NT") ? atoi(getenv("GPUPROBE_GEMM_NT")) : 0;
+  p->nt = (p->cg == 2 && n % 512 == 0 && env_nt != 1) ? 2 : 1;
   if (m % 256 || n % 256 || k % 64 || m == 0 || n == 0 || k == 0) {
     set_error("gemm needs m, n multiples of 256 and k a multiple of 64");
     return GP_ERR_INVALID;
@@ -544,8 +565,9 @@ static int make_plan(GemmPlan* p, const void* A, const void* B, const void* C, u
 
 static cudaError_t launch_gemm(const GemmPlan& p, float* C, int M, int N, int K, int sm_count,
                                cudaStream_t stream) {
-  return p.cg == 2 ? launch_gemm_cg<2>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
-                   : launch_gemm_cg<1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+  if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+  return p.cg == 2 ? launch_gemm_cg<2, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
+                   : launch_gemm_cg<1, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
 }
 
 #define CU_OR_RETURN(call)                                               \
