@@ -108,12 +108,12 @@ typedef struct gp_config {
   uint32_t gemm_samples;   /* sampled C entries checked on the host in fp64; 0 -> 4096 */
   uint32_t stream_variant; /* GP_STREAM_* */
   uint32_t keep_arena;     /* 1: keep device memory between probes; 0: free after gp_probe_* */
-  uint32_t reserved0;
+  uint32_t gemm_output;    /* GEMM probe's C: 0 = fp32 (strictest check), 1 = bf16 (what cuBLAS bf16 peaks are quoted on) */
   uint64_t seed;           /* GEMM / triad operand generator seed; 0 -> 0x5EED */
   double min_copy_gbps;    /* health floors; 0 -> not enforced */
   double min_triad_gbps;
   double min_gemm_tflops;
-  double gemm_tol;         /* |c-ref| <= gemm_tol * sum_k|a||b|; 0 -> 1e-3 */
+  double gemm_tol;         /* |c-ref| <= gemm_tol * sum_k|a||b| (+ 2^-8 |ref| for bf16 output); 0 -> 1e-3 */
 } gp_config;
 
 /* One verify pass — SURVEY.md §8(c).  All sums are mod 2^64. */
@@ -144,7 +144,9 @@ typedef struct gp_gemm_result {
   double freivalds_err;    /* max_i |(C x)_i - (A (B^T x))_i| / (sum_j sum_k |a||b||x|) */
   uint32_t samples;
   uint32_t samples_bad;    /* samples exceeding gemm_tol */
-  uint64_t c_checksum;     /* XOR of the fp32 bit patterns of C folded to 64 bit */
+  uint64_t c_checksum;     /* XOR of C's bit patterns folded to 64 bit */
+  uint32_t output_bf16;    /* 1 if C was bf16: errors are then measured beyond the 2^-8 |ref| output rounding */
+  uint32_t reserved;
 } gp_gemm_result;
 
 typedef struct gp_device_result {

@@ -205,7 +205,8 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
 }
 
 // ---------------------------------------------------------------- kernel ---
-template <int CG, int NT>
+// OUT = 0: C is fp32; OUT = 1: C is bf16 (round-to-nearest-even of the fp32 accumulator)
+template <int CG, int NT, int OUT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_c, float* __restrict__ C, int M, int N, int K,
@@ -335,7 +336,44 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const int row = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32 + lane;
       float* crow = C + (size_t)row * N + (size_t)tn * Cfg::kTileNAll;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * Cfg::kTileNAll);
-      if (hints & 128) {  // development path: direct 256-bit stores from registers
+      if constexpr (OUT == 1) {
+        // bf16 output: 64 accumulator columns -> one 128-byte staging row per lane -> TMA store of a
+        // 32 x 64 bf16 box; same swizzle and double buffering as the fp32 path below
+        const int ewarp = warp - 2;
+        const int tile_row0 = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32;
+#pragma unroll 1
+        for (int c = 0; c < Cfg::kTileNAll / 64; ++c) {
+          float v0[32], v1[32];
+          tmem_ld_32x32(taddr + (uint32_t)(c * 64), v0);
+          tmem_ld_32x32(taddr + (uint32_t)(c * 64 + 32), v1);
+          const uint32_t buf = epi_base + (uint32_t)(((epi_count & 1) * 4 + ewarp) * 4096);
+          if (lane == 0) bulk_wait_read<1>();
+          __syncwarp();
+          tmem_ld_wait();
+          uint32_t w[32];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[i]) : "f"(v0[2 * i + 1]), "f"(v0[2 * i]));
+            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[16 + i]) : "f"(v1[2 * i + 1]), "f"(v1[2 * i]));
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t addr = buf + (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4));
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(w[4 * j]), "r"(w[4 * j + 1]),
+                         "r"(w[4 * j + 2]), "r"(w[4 * j + 3]) : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            asm volatile(
+                "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(&map_c),
+                "r"(buf), "r"(tn * Cfg::kTileNAll + c * 64), "r"(tile_row0), "l"(pol_c)
+                : "memory");
+            bulk_commit();
+          }
+          ++epi_count;
+        }
+      } else if (hints & 128) {  // development path: direct 256-bit stores from registers
 #pragma unroll 1
         for (int c = 0; c < Cfg::kTileNAll / 32; ++c) {
           float v[32];
@@ -394,11 +432,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 }
 
 // --------------------------------------------------- check / helper kernels --
+__device__ __forceinline__ float c_load(const float* C, size_t i) { return C[i]; }
+__device__ __forceinline__ float c_load(const uint16_t* C, size_t i) { return bf16_bits_to_f32(C[i]); }
 // gather sampled entries of C
-__global__ void gather_kernel(const float* __restrict__ C, int N, const uint32_t* __restrict__ ij,
+template <class T>
+__global__ void gather_kernel(const T* __restrict__ C, int N, const uint32_t* __restrict__ ij,
                               int n, float* __restrict__ out) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n) out[t] = C[(size_t)ij[2 * t] * N + ij[2 * t + 1]];
+  if (t < n) out[t] = c_load(C, (size_t)ij[2 * t] * N + ij[2 * t + 1]);
 }
 // Freivalds in fp64 on the CUDA cores: x_j = +-1 from the generator.
 __global__ void fv_signs_kernel(float* __restrict__ x, int N, uint64_t seed) {
@@ -421,29 +462,34 @@ __global__ void fv_bt_x_kernel(const uint16_t* __restrict__ B, int N, int K, con
   atomicAdd(&u[k], s);
   atomicAdd(&ub[k], a);
 }
-// v[i] = SUM_k A[i][k] u[k] ; sc[i] = SUM_k |A[i][k]| ub[k] ; w[i] = SUM_j C[i][j] x[j]   (one warp per row)
-__global__ void fv_rows_kernel(const uint16_t* __restrict__ A, const float* __restrict__ C, int M, int N,
+// v[i] = SUM_k A[i][k] u[k] ; sc[i] = SUM_k |A[i][k]| ub[k] ; w[i] = SUM_j C[i][j] x[j] ;
+// cabs[i] = SUM_j |C[i][j]|   (one warp per row)
+template <class T>
+__global__ void fv_rows_kernel(const uint16_t* __restrict__ A, const T* __restrict__ C, int M, int N,
                                int K, const float* __restrict__ x, const double* __restrict__ u,
                                const double* __restrict__ ub, double* __restrict__ v,
-                               double* __restrict__ sc, double* __restrict__ w) {
+                               double* __restrict__ sc, double* __restrict__ w, double* __restrict__ cabs) {
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (row >= M) return;
-  double sv = 0, ss = 0, sw = 0;
+  double sv = 0, ss = 0, sw = 0, sa = 0;
   for (int k = lane; k < K; k += 32) {
     const double a = (double)bf16_bits_to_f32(A[(size_t)row * K + k]);
     sv += a * u[k];
     ss += fabs(a) * ub[k];
   }
   for (int j = lane; j < N; j += 32) {
-    sw += (double)C[(size_t)row * N + j] * (double)x[j];
+    const double cv = (double)c_load(C, (size_t)row * N + j);
+    sw += cv * (double)x[j];
+    sa += fabs(cv);
   }
 #pragma unroll
   for (int m = 16; m > 0; m >>= 1) {
     sv += __shfl_xor_sync(0xffffffffu, sv, m);
     ss += __shfl_xor_sync(0xffffffffu, ss, m);
     sw += __shfl_xor_sync(0xffffffffu, sw, m);
+    sa += __shfl_xor_sync(0xffffffffu, sa, m);
   }
-  if (lane == 0) { v[row] = sv; sc[row] = ss; w[row] = sw; }
+  if (lane == 0) { v[row] = sv; sc[row] = ss; w[row] = sw; cabs[row] = sa; }
 }
 
 // ------------------------------------------------------------------ host ----
@@ -485,7 +531,7 @@ static int gemm_cta_group() {
   return 2;
 }
 
-template <int CG, int NT>
+template <int CG, int NT, int OUT>
 static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, float* C,
                                   int M, int N, int K, int sm_count, cudaStream_t stream) {
   using Cfg = GemmCfg<CG, NT>;
@@ -512,42 +558,49 @@ static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, 
   // measured at 8192^3, 20 launches each: operands evict_last + C evict_first 1462 TFLOP/s median,
   // no hints 1438; operand panels are re-read by the next wave, C is written once and never read
   const int hints = env_hints >= 0 ? env_hints : (1 | (1 << 2) | (2 << 4));
-  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG, NT>, ma, mb, mc, C, M, N, K, group_m, hints);
+  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG, NT, OUT>, ma, mb, mc, C, M, N, K, group_m, hints);
 }
 
 // function attributes are per device: called once from device_prepare with the device current
+template <int CG, int NT, int OUT>
+static cudaError_t configure_one() {
+  return cudaFuncSetAttribute(gemm_bf16_kernel<CG, NT, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)GemmCfg<CG, NT>::kSmemBytes);
+}
 cudaError_t gemm_kernels_configure() {
-  cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)GemmCfg<1, 1>::kSmemBytes);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(gemm_bf16_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)GemmCfg<2, 1>::kSmemBytes);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(gemm_bf16_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)GemmCfg<2, 2>::kSmemBytes);
+  cudaError_t e;
+  if ((e = configure_one<1, 1, 0>()) != cudaSuccess) return e;
+  if ((e = configure_one<2, 1, 0>()) != cudaSuccess) return e;
+  if ((e = configure_one<2, 2, 0>()) != cudaSuccess) return e;
+  if ((e = configure_one<1, 1, 1>()) != cudaSuccess) return e;
+  if ((e = configure_one<2, 1, 1>()) != cudaSuccess) return e;
+  return configure_one<2, 2, 1>();
 }
 
 struct GemmPlan {
-  int cg, nt;
+  int cg, nt, out;
   CUtensorMap ma, mb, mc;
 };
 
-// C (fp32, row-major M x N) as a 2-D map with a 32 x 32 box (128-byte rows) and 128-byte swizzle
-static int make_map_c(CUtensorMap* map, const void* base, uint64_t M, uint64_t N) {
+// C (row-major M x N) as a 2-D map with 128-byte box rows (32 fp32 or 64 bf16) x 32 rows, 128-byte swizzle
+static int make_map_c(CUtensorMap* map, const void* base, uint64_t M, uint64_t N, bool out_bf16) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return GP_ERR_UNSUPPORTED; }
   const cuuint64_t dims[2] = {N, M};
-  const cuuint64_t strides[1] = {N * 4};
-  const cuuint32_t box[2] = {32, 32};
+  const cuuint64_t strides[1] = {N * (out_bf16 ? 2u : 4u)};
+  const cuuint32_t box[2] = {out_bf16 ? 64u : 32u, 32};
   const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+  const CUresult r = enc(map, out_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                         const_cast<void*>(base), dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (C) failed: %d", (int)r); return GP_ERR_CUDA; }
   return GP_OK;
 }
 
-static int make_plan(GemmPlan* p, const void* A, const void* B, const void* C, uint32_t m, uint32_t n, uint32_t k) {
+static int make_plan(GemmPlan* p, const void* A, const void* B, const void* C, uint32_t m, uint32_t n, uint32_t k,
+                     bool out_bf16) {
+  p->out = out_bf16 ? 1 : 0;
   p->cg = gemm_cta_group();
   // 256 x 512 tiles (two N sub-tiles per CTA pair) whenever the shape allows; GPUPROBE_GEMM_NT=1 forces 256 x 256
   static const int env_nt = getenv("GPUPROBE_GEMM_NT") ? atoi(getenv("GPUPROBE_GEMM_NT")) : 0;
@@ -558,16 +611,21 @@ static int make_plan(GemmPlan* p, const void* A, const void* B, const void* C, u
   }
   int rc = make_map(&p->ma, A, m, k, kBlockM);
   if (rc) return rc;
-  rc = make_map_c(&p->mc, C, m, n);
+  rc = make_map_c(&p->mc, C, m, n, out_bf16);
   if (rc) return rc;
   return make_map(&p->mb, B, n, k, (uint32_t)(kTileN / p->cg));
 }
 
 static cudaError_t launch_gemm(const GemmPlan& p, float* C, int M, int N, int K, int sm_count,
                                cudaStream_t stream) {
-  if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
-  return p.cg == 2 ? launch_gemm_cg<2, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
-                   : launch_gemm_cg<1, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+  if (p.out) {
+    if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+    return p.cg == 2 ? launch_gemm_cg<2, 1, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
+                     : launch_gemm_cg<1, 1, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+  }
+  if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2, 0>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+  return p.cg == 2 ? launch_gemm_cg<2, 1, 0>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
+                   : launch_gemm_cg<1, 1, 0>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
 }
 
 #define CU_OR_RETURN(call)                                               \
@@ -597,7 +655,7 @@ int gemm_host_locked(Ctx* ctx, Device* d, const uint16_t* a, const uint16_t* b, 
   uint8_t* B = A + up(a_bytes);
   float* C = reinterpret_cast<float*>(B + up(b_bytes));
   GemmPlan plan;
-  rc = make_plan(&plan, A, B, C, m, n, k);
+  rc = make_plan(&plan, A, B, C, m, n, k, /*out_bf16=*/false);
   if (rc) return rc;
   CU_OR_RETURN(cudaMemcpyAsync(A, a, a_bytes, cudaMemcpyHostToDevice, d->stream));
   CU_OR_RETURN(cudaMemcpyAsync(B, b, b_bytes, cudaMemcpyHostToDevice, d->stream));
@@ -619,10 +677,12 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   out->m = m; out->n = n; out->k = k;
   if (iters + 1 > (uint32_t)kEventPool) return GP_ERR_TOO_LARGE;
   if (samples > 65536) samples = 65536;
-  const size_t a_bytes = (size_t)m * k * 2, b_bytes = (size_t)n * k * 2, c_bytes = (size_t)m * n * 4;
+  const bool out_bf16 = ctx->cfg.gemm_output == 1;
+  out->output_bf16 = out_bf16 ? 1 : 0;
+  const size_t a_bytes = (size_t)m * k * 2, b_bytes = (size_t)n * k * 2, c_bytes = (size_t)m * n * (out_bf16 ? 2 : 4);
   auto up = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
   const size_t vec_bytes = up((size_t)std::max(std::max(m, n), k) * sizeof(double));
-  const size_t aux = 6 * vec_bytes + up((size_t)samples * 8) + up((size_t)samples * 4);
+  const size_t aux = 7 * vec_bytes + up((size_t)samples * 8) + up((size_t)samples * 4);
   rc = ensure_arena(ctx, d, up(a_bytes) + up(b_bytes) + up(c_bytes) + aux);
   if (rc) return rc;
   d->triad_operands_bytes = 0;
@@ -635,12 +695,13 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   double* v = reinterpret_cast<double*>(p); p += vec_bytes;
   double* sc = reinterpret_cast<double*>(p); p += vec_bytes;
   double* w = reinterpret_cast<double*>(p); p += vec_bytes;
+  double* cabs = reinterpret_cast<double*>(p); p += vec_bytes;
   float* xs = reinterpret_cast<float*>(p); p += vec_bytes;
   uint32_t* d_ij = reinterpret_cast<uint32_t*>(p); p += up((size_t)samples * 8);
   float* d_sampled = reinterpret_cast<float*>(p);
 
   GemmPlan plan;
-  rc = make_plan(&plan, A, B, C, m, n, k);
+  rc = make_plan(&plan, A, B, C, m, n, k, out_bf16);
   if (rc) return rc;
   cudaStream_t s = d->stream;
   CU_OR_RETURN(launch_gen_bf16(A, (uint64_t)m * k, seed, d->sm_count, s));
@@ -666,7 +727,10 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   std::vector<float> got(samples);
   if (samples) {
     CU_OR_RETURN(cudaMemcpyAsync(d_ij, ij.data(), ij.size() * 4, cudaMemcpyHostToDevice, s));
-    gather_kernel<<<(samples + 255) / 256, 256, 0, s>>>(C, (int)n, d_ij, (int)samples, d_sampled);
+    if (out_bf16)
+      gather_kernel<uint16_t><<<(samples + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint16_t*>(C), (int)n, d_ij, (int)samples, d_sampled);
+    else
+      gather_kernel<float><<<(samples + 255) / 256, 256, 0, s>>>(C, (int)n, d_ij, (int)samples, d_sampled);
     CU_OR_RETURN(cudaGetLastError());
     CU_OR_RETURN(cudaMemcpyAsync(got.data(), d_sampled, (size_t)samples * 4, cudaMemcpyDeviceToHost, s));
   }
@@ -674,9 +738,13 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   CU_OR_RETURN(cudaMemsetAsync(u, 0, 2 * vec_bytes, s));  // u and ub are adjacent
   fv_bt_x_kernel<<<dim3((k + 127) / 128, 32), 128, 0, s>>>(B, (int)n, (int)k, xs, u, ub);
   CU_OR_RETURN(cudaGetLastError());
-  fv_rows_kernel<<<(m * 32 + 255) / 256, 256, 0, s>>>(A, C, (int)m, (int)n, (int)k, xs, u, ub, v, sc, w);
+  if (out_bf16)
+    fv_rows_kernel<uint16_t><<<(m * 32 + 255) / 256, 256, 0, s>>>(A, reinterpret_cast<const uint16_t*>(C), (int)m, (int)n, (int)k, xs, u, ub, v, sc, w, cabs);
+  else
+    fv_rows_kernel<float><<<(m * 32 + 255) / 256, 256, 0, s>>>(A, C, (int)m, (int)n, (int)k, xs, u, ub, v, sc, w, cabs);
   CU_OR_RETURN(cudaGetLastError());
-  std::vector<double> hv(m), hs(m), hw(m);
+  std::vector<double> hv(m), hs(m), hw(m), hc(m);
+  CU_OR_RETURN(cudaMemcpyAsync(hc.data(), cabs, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
   CU_OR_RETURN(cudaMemcpyAsync(hv.data(), v, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
   CU_OR_RETURN(cudaMemcpyAsync(hs.data(), sc, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
   CU_OR_RETURN(cudaMemcpyAsync(hw.data(), w, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
@@ -704,6 +772,7 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
 
   // host reference of the sampled entries: fp64 dot products of the bf16-rounded generator output
   const double tol = ctx->cfg.gemm_tol > 0 ? ctx->cfg.gemm_tol : 1e-3;
+  const double out_round = out_bf16 ? 1.0 / 256.0 : 0.0;
   std::vector<double> err(samples, 0.0);
   const unsigned nthreads = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
   std::vector<std::thread> th;
@@ -718,7 +787,8 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
           acc += x * y;
           aacc += fabs(x * y);
         }
-        const double e = fabs((double)got[t] - acc);
+        // a bf16 result may differ from the exact value by its own rounding, 2^-8 |ref| at most
+        const double e = std::max(0.0, fabs((double)got[t] - acc) - out_round * fabs(acc));
         err[t] = (std::isfinite((double)got[t]) && aacc > 0) ? e / aacc : (e == 0 ? 0.0 : 1e30);
       }
     });
@@ -730,7 +800,7 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
     if (!(err[t] <= tol)) out->samples_bad++;
   }
   for (uint32_t i = 0; i < m; ++i) {
-    const double e = fabs(hw[i] - hv[i]);
+    const double e = std::max(0.0, fabs(hw[i] - hv[i]) - out_round * hc[i]);
     const double r = (std::isfinite(hw[i]) && hs[i] > 0) ? e / hs[i] : (e == 0 ? 0.0 : 1e30);
     out->freivalds_err = std::max(out->freivalds_err, r);
   }

@@ -47,7 +47,7 @@ class Config(C.Structure):
         ("hbm_bytes", C.c_uint64), ("pattern_bytes", C.c_uint64), ("arena_cap_bytes", C.c_uint64),
         ("gemm_mnk", C.c_uint32), ("warmup", C.c_uint32), ("iters", C.c_uint32),
         ("wo_passes", C.c_uint32), ("gemm_samples", C.c_uint32), ("stream_variant", C.c_uint32),
-        ("keep_arena", C.c_uint32), ("reserved0", C.c_uint32),
+        ("keep_arena", C.c_uint32), ("gemm_output", C.c_uint32),
         ("seed", C.c_uint64),
         ("min_copy_gbps", C.c_double), ("min_triad_gbps", C.c_double),
         ("min_gemm_tflops", C.c_double), ("gemm_tol", C.c_double),
@@ -73,7 +73,8 @@ class GemmResult(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("m", C.c_uint32), ("n", C.c_uint32), ("k", C.c_uint32),
                 ("t", Timing), ("tflops_best", C.c_double), ("tflops_median", C.c_double),
                 ("max_scaled_err", C.c_double), ("freivalds_err", C.c_double),
-                ("samples", C.c_uint32), ("samples_bad", C.c_uint32), ("c_checksum", C.c_uint64)]
+                ("samples", C.c_uint32), ("samples_bad", C.c_uint32), ("c_checksum", C.c_uint64),
+                ("output_bf16", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class DeviceResult(C.Structure):

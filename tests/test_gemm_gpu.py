@@ -116,3 +116,17 @@ def test_gemm_golden_points(probe, oracle, cta_group):
         probe.gemm_host(DEV, a, b, c, n, n, n)
         for pt in g["points"]:
             assert abs(float(c[pt["i"], pt["j"]]) - pt["ref"]) <= TOL * pt["absdot"], pt
+
+
+def test_gemm_probe_bf16_output(cta_group):
+    """C in bf16 (gp_config.gemm_output = 1): same checks, errors measured beyond the 2^-8 |ref|
+    rounding of the output itself; the fp32-output run of the same problem stays the strict one."""
+    with gpuprobe.Probe(keep_arena=1, gemm_output=1) as p:
+        for mnk in (1024, 2048, 8192):
+            g = p.gemm_probe(DEV, mnk=mnk, iters=3, warmup=1, samples=4096)
+            print(f"gemm probe bf16-out {mnk}^3 cta_group={cta_group}: {g.tflops_best:.0f} TFLOP/s best, "
+                  f"max scaled err {g.max_scaled_err:.2e}, freivalds {g.freivalds_err:.2e}")
+            assert g.output_bf16 == 1 and g.samples_bad == 0
+            assert g.max_scaled_err <= TOL and g.freivalds_err <= TOL
+    with gpuprobe.Probe(keep_arena=1) as p:
+        assert p.gemm_probe(DEV, mnk=1024, iters=1, warmup=0, samples=64).output_bf16 == 0
