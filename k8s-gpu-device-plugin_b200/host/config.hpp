@@ -22,6 +22,7 @@ struct ProbeConfig {
   uint64_t HbmBytes = 16ull << 30;  // BASELINE.json configs[1]
   uint32_t WoPasses = 64;
   uint32_t GemmMNK = 8192;
+  std::string GemmOutput = "fp32";  // "fp32" (strictest check) or "bf16" (what cuBLAS bf16 peaks write)
   double MinCopyGbps = 0, MinTriadGbps = 0, MinGemmTflops = 0;  // 0 = floor not enforced
   int IntervalSeconds = 0;                                       // 0 = no periodic re-probe
 };
@@ -39,6 +40,7 @@ struct Config {
     c.hbm_bytes = Probe.HbmBytes;
     c.wo_passes = Probe.WoPasses;
     c.gemm_mnk = Probe.GemmMNK;
+    c.gemm_output = Probe.GemmOutput == "bf16" ? 1u : 0u;
     c.min_copy_gbps = Probe.MinCopyGbps;
     c.min_triad_gbps = Probe.MinTriadGbps;
     c.min_gemm_tflops = Probe.MinGemmTflops;
@@ -94,6 +96,7 @@ inline Config LoadConfig(const std::string& yamlText) {
   if (auto v = get("probe.hbmBytes")) c.Probe.HbmBytes = std::stoull(*v);
   if (auto v = get("probe.woPasses")) c.Probe.WoPasses = (uint32_t)std::stoul(*v);
   if (auto v = get("probe.gemmMNK")) c.Probe.GemmMNK = (uint32_t)std::stoul(*v);
+  if (auto v = get("probe.gemmOutput")) c.Probe.GemmOutput = *v;
   if (auto v = get("probe.minCopyGbps")) c.Probe.MinCopyGbps = std::stod(*v);
   if (auto v = get("probe.minTriadGbps")) c.Probe.MinTriadGbps = std::stod(*v);
   if (auto v = get("probe.minGemmTflops")) c.Probe.MinGemmTflops = std::stod(*v);

@@ -243,7 +243,8 @@ int main() {
     Config e3 = LoadConfig(std::string(ref_yml) + "probe:\n  enabled: true\n  hbmBytes: 1073741824   # 1 GiB\n  minCopyGbps: 6000\n  intervalSeconds: 300\n");
     CHECK(e3.Probe.HbmBytes == (1ull << 30) && e3.Probe.MinCopyGbps == 6000 && e3.Probe.IntervalSeconds == 300 && e3.MigStrategy == "none");
     gp_config g = e3.ToGpConfig();
-    CHECK(g.struct_size == sizeof(gp_config) && g.hbm_bytes == (1ull << 30) && g.min_copy_gbps == 6000);
+    CHECK(g.struct_size == sizeof(gp_config) && g.hbm_bytes == (1ull << 30) && g.min_copy_gbps == 6000 && g.gemm_output == 0);
+    CHECK(LoadConfig("probe:\n  gemmOutput: bf16\n").ToGpConfig().gemm_output == 1);
   }
   printf("host_selftest ok\n");
   return 0;
