@@ -139,8 +139,8 @@ def dist_env():
 
 
 # ------------------------------------------------------------------ CPU port ----------------
-def cpu_port_run(nbytes, steps, warmup, min_seconds=0.0, max_seconds=30.0):
-    """Times the CPU port of the step (oracle/) with every host thread.  Returns a dict."""
+def cpu_port_run(nbytes, steps, warmup, min_seconds=0.0, max_seconds=30.0, threads=None):
+    """Times the CPU port of the step (oracle/) with every host thread (or `threads`).  Returns a dict."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import numpy as np
     import oracle_lib
@@ -150,6 +150,8 @@ def cpu_port_run(nbytes, steps, warmup, min_seconds=0.0, max_seconds=30.0):
         cores = len(os.sched_getaffinity(0))
     except Exception:
         pass
+    if threads:
+        cores = threads
     arena = np.zeros(5 * nbytes, dtype=np.uint8)  # first touch here
     nwords = nbytes // 8
     for w in range(max(warmup, 1)):
@@ -465,8 +467,9 @@ def run_ours(args):
         line["e2e_host_buffer"] = e2e_host
     if n_gpus == 1 and not args.no_cpu:
         c = cpu_port_run(args.cpu_bytes, 1, 1, min_seconds=10.0, max_seconds=30.0)
+        c1 = cpu_port_run(args.cpu_bytes, 1, 1, min_seconds=3.0, max_seconds=8.0, threads=1)
         line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
-                                "sample": c["sample"],
+                                "sample": c["sample"], "value_1_thread": c1["value"],
                                 "note": "CPU port of the frozen spec (oracle/); the reference has no "
                                         "code for this path"}
     print(json.dumps(line), flush=True)

@@ -316,7 +316,8 @@ int gp_inject_bitflip(gp_ctx* ctx, const char* uuid, uint64_t word_index, int bi
  * gbps is n*n row-major, row = src; diagonal = local bandwidth.
  * dir 3 = all pairs at once (switch saturation): every GPU reads `bytes` from
  * each peer concurrently; row i = GPU i's aggregate ingress / (n-1), diagonal =
- * the aggregate. */
+ * the aggregate.  dir 4 = bidirectional read (both GPUs of a pair read from each
+ * other at once). */
 int gp_probe_p2p(gp_ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps);
 /* In-place fp32 sum ncclAllReduce over the first nranks devices. */
 int gp_probe_allreduce(gp_ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters,

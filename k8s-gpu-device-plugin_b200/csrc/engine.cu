@@ -809,7 +809,7 @@ int gp_inject_bitflip(gp_ctx* ctx, const char* uuid, uint64_t word_index, int bi
 }
 
 int gp_probe_p2p(gp_ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps_out) {
-  if (!ctx || !gbps_out || ngpus < 1 || dir < 0 || dir > 3) { set_error("bad arguments"); return GP_ERR_INVALID; }
+  if (!ctx || !gbps_out || ngpus < 1 || dir < 0 || dir > 4) { set_error("bad arguments"); return GP_ERR_INVALID; }
   return p2p_probe(ctx, ngpus, bytes, dir, gbps_out);
 }
 

@@ -320,7 +320,7 @@ int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
       for (int i = 0; i < ngpus; ++i) free_arena(ctx->devs[(size_t)i].get());
     return GP_OK;
   }
-  const bool write = dir != 0;
+  const bool write = dir == 1 || dir == 2;
   const int iters = 3;
   std::vector<double> r;
   // diagonal: the same kernel on local memory, all GPUs at once
@@ -332,10 +332,10 @@ int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
     for (int i = 0; i < ngpus; ++i) gbps[i * ngpus + i] = r[(size_t)i];
   }
   for (const auto& round : rounds_for(ngpus)) {
-    if (dir == 2) {
+    if (dir == 2 || dir == 4) {  // both directions of every pair at once: 2 = writes, 4 = reads
       std::vector<Xfer> xs;
       for (auto pr : round) { xs.push_back({pr.first, pr.second}); xs.push_back({pr.second, pr.first}); }
-      int rc = run_xfers(ctx, xs, bytes, true, iters, &r);
+      int rc = run_xfers(ctx, xs, bytes, dir == 2, iters, &r);
       if (rc) return rc;
       for (size_t i = 0; i < xs.size(); ++i) gbps[xs[i].src * ngpus + xs[i].dst] = r[i];
     } else {

@@ -15,7 +15,7 @@ p = gpuprobe.Probe(keep_arena=1, arena_cap_bytes=8 << 30)
 n = int(sys.argv[1]) if len(sys.argv) > 1 else p.device_count()
 out = {"n_gpus": n, "p2p": {}, "allreduce": {}}
 sizes = [64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30]
-for name, d in (("read", 0), ("write", 1), ("bidir_write", 2), ("all_at_once_read", 3)):
+for name, d in (("read", 0), ("write", 1), ("bidir_write", 2), ("bidir_read", 4), ("all_at_once_read", 3)):
     out["p2p"][name] = {}
     for s in sizes:
         m = p.probe_p2p(n, s, d)
