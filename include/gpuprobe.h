@@ -95,11 +95,14 @@ enum {
   GP_STREAM_TMA = 2  /* cp.async.bulk global->smem->global, mbarrier pipeline */
 };
 
+#define GP_PATTERN_ALL_FREE UINT64_MAX
+
 typedef struct gp_config {
   uint32_t struct_size;    /* = sizeof(gp_config) */
   uint32_t abi_version;    /* = GP_ABI_VERSION */
   uint64_t hbm_bytes;      /* bytes per stream array; 0 -> 16 GiB (BASELINE.json configs[1]) */
-  uint64_t pattern_bytes;  /* bytes graded by fill/verify; 0 -> hbm_bytes */
+  uint64_t pattern_bytes;  /* bytes graded by fill/verify; 0 -> hbm_bytes; GP_PATTERN_ALL_FREE -> every free
+                            * byte of the device but a 1 GiB margin (whole-memory grading) */
   uint64_t arena_cap_bytes;/* hard cap for the per-device arena; 0 -> 5*hbm_bytes + 1 GiB */
   uint32_t gemm_mnk;       /* M=N=K of the GEMM probe; 0 -> 8192 */
   uint32_t warmup;         /* untimed launches per kernel; 0 -> 2 */

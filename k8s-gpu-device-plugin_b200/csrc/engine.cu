@@ -144,9 +144,9 @@ static uint64_t cfg_arena_cap(const Ctx* c) {
   return c->cfg.arena_cap_bytes ? c->cfg.arena_cap_bytes : 5 * cfg_hbm_bytes(c) + (1ull << 30);
 }
 
-int ensure_arena(Ctx* ctx, Device* d, size_t bytes) {
+int ensure_arena(Ctx* ctx, Device* d, size_t bytes, bool ignore_cap) {
   if (bytes <= d->arena_bytes) return GP_OK;
-  if (bytes > cfg_arena_cap(ctx)) {
+  if (!ignore_cap && bytes > cfg_arena_cap(ctx)) {
     set_error("arena request %zu exceeds cap %llu", bytes, (unsigned long long)cfg_arena_cap(ctx));
     return GP_ERR_NOMEM;
   }
@@ -347,7 +347,17 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
   const uint32_t warmup = ctx->cfg.warmup ? ctx->cfg.warmup : 2;
   const uint32_t iters = ctx->cfg.iters ? ctx->cfg.iters : 10;
   const uint64_t hbm = cfg_hbm_bytes(ctx);
-  const uint64_t pat = cfg_pattern_bytes(ctx);
+  uint64_t pat = cfg_pattern_bytes(ctx);
+  const bool pat_all = pat == GP_PATTERN_ALL_FREE;
+  if (pat_all) {
+    // whole-memory grading: everything the driver will still give us, minus a margin, in 1 MiB units
+    size_t free_b = 0, total_b = 0;
+    free_arena(d);
+    cudaError_t e = cudaMemGetInfo(&free_b, &total_b);
+    if (e != cudaSuccess) { out->error = cuda_fail(e, "cudaMemGetInfo", &out->detail); return out->error; }
+    const uint64_t margin = 1ull << 30;
+    pat = free_b > 2 * margin ? ((uint64_t)free_b - margin) & ~((1ull << 20) - 1) : 0;
+  }
   out->hbm_bytes = hbm;
   out->pattern_bytes = pat;
   int rc = GP_OK;
@@ -369,8 +379,8 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
       const uint64_t g = ctx->cfg.gemm_mnk ? ctx->cfg.gemm_mnk : 8192;
       need = std::max<uint64_t>(need, 8 * g * g + (4ull << 20));  // A + B (2 B) + C (4 B) + check vectors
     }
-    if (need > d->arena_bytes && need <= cfg_arena_cap(ctx)) {
-      rc = ensure_arena(ctx, d, need);
+    if (need > d->arena_bytes && (need <= cfg_arena_cap(ctx) || pat_all)) {
+      rc = ensure_arena(ctx, d, need, /*ignore_cap=*/pat_all);
       if (rc) return fail(rc);
     }
   }
@@ -396,7 +406,7 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
   }
   if (mask & GP_PROBE_PATTERN) {
     if (pat == 0 || (pat % 512)) { set_error("pattern_bytes must be a multiple of 512"); return fail(GP_ERR_INVALID); }
-    rc = ensure_arena(ctx, d, pat);
+    rc = ensure_arena(ctx, d, pat, pat_all);
     if (rc) return fail(rc);
     d->triad_operands_bytes = 0;
     const uint64_t nwords = pat / 8;

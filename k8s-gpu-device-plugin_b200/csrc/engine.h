@@ -55,7 +55,7 @@ int cuda_fail(cudaError_t e, const char* what, int64_t* detail);
 
 Device* find_device(Ctx* ctx, const char* uuid);
 int device_prepare(Ctx* ctx, Device* d);                  // lazy per-device init, lock held
-int ensure_arena(Ctx* ctx, Device* d, size_t bytes);      // lock held
+int ensure_arena(Ctx* ctx, Device* d, size_t bytes, bool ignore_cap = false);  // lock held
 void free_arena(Device* d);
 int resolve_variant(const Ctx* ctx);
 

@@ -163,6 +163,7 @@ def load(path: Optional[str] = None) -> C.CDLL:
 
 
 GP_NOALLOC_MAX_WORDS = 1 << 35
+GP_PATTERN_ALL_FREE = (1 << 64) - 1
 
 
 def pattern_verify_noalloc(ordinal: int, d_words_ptr: int, nwords: int, kind: int, pas: int,

@@ -89,3 +89,12 @@ def test_nvml_snapshot():
         assert i.other_compute_procs == 0  # a fresh box: nobody else is computing here
         with pytest.raises(gpuprobe.GpuProbeError):
             p.nvml_snapshot("GPU-00000000-0000-0000-0000-000000000000")
+
+
+def test_whole_memory_grading():
+    """pattern_bytes = GP_PATTERN_ALL_FREE: fill/verify every free byte but a 1 GiB margin."""
+    with gpuprobe.Probe(pattern_bytes=gpuprobe.GP_PATTERN_ALL_FREE, wo_passes=2) as p:
+        r = p.probe_device("0", gpuprobe.GP_PROBE_PATTERN)
+        assert r.healthy == 1 and r.pattern_passes == 4 and r.pattern_mismatches == 0
+        assert r.pattern_bytes > (100 << 30) and r.pattern_bytes % (1 << 20) == 0  # most of the 180 GB card
+        assert r.verify_gbps_best > 1000 and r.fill_gbps_best > 1000
