@@ -20,6 +20,7 @@ struct LogConfig { std::string Level = "debug", FileDir; };
 struct ProbeConfig {
   bool Enabled = true;
   uint64_t HbmBytes = 16ull << 30;  // BASELINE.json configs[1]
+  uint64_t PatternBytes = 0;        // 0 = same as HbmBytes; GP_PATTERN_ALL_FREE ("all" in the file) = whole memory
   uint32_t WoPasses = 64;
   uint32_t GemmMNK = 8192;
   std::string GemmOutput = "fp32";  // "fp32" (strictest check) or "bf16" (what cuBLAS bf16 peaks write)
@@ -38,6 +39,7 @@ struct Config {
     c.struct_size = sizeof(c);
     c.abi_version = GP_ABI_VERSION;
     c.hbm_bytes = Probe.HbmBytes;
+    c.pattern_bytes = Probe.PatternBytes;
     c.wo_passes = Probe.WoPasses;
     c.gemm_mnk = Probe.GemmMNK;
     c.gemm_output = Probe.GemmOutput == "bf16" ? 1u : 0u;
@@ -94,6 +96,7 @@ inline Config LoadConfig(const std::string& yamlText) {
   if (auto v = get("log.fileDir")) c.Log.FileDir = *v;
   if (auto v = get("probe.enabled")) c.Probe.Enabled = truthy(*v);
   if (auto v = get("probe.hbmBytes")) c.Probe.HbmBytes = std::stoull(*v);
+  if (auto v = get("probe.patternBytes")) c.Probe.PatternBytes = (*v == "all") ? GP_PATTERN_ALL_FREE : std::stoull(*v);
   if (auto v = get("probe.woPasses")) c.Probe.WoPasses = (uint32_t)std::stoul(*v);
   if (auto v = get("probe.gemmMNK")) c.Probe.GemmMNK = (uint32_t)std::stoul(*v);
   if (auto v = get("probe.gemmOutput")) c.Probe.GemmOutput = *v;

@@ -245,6 +245,7 @@ int main() {
     gp_config g = e3.ToGpConfig();
     CHECK(g.struct_size == sizeof(gp_config) && g.hbm_bytes == (1ull << 30) && g.min_copy_gbps == 6000 && g.gemm_output == 0);
     CHECK(LoadConfig("probe:\n  gemmOutput: bf16\n").ToGpConfig().gemm_output == 1);
+    CHECK(LoadConfig("probe:\n  patternBytes: all\n").ToGpConfig().pattern_bytes == GP_PATTERN_ALL_FREE);
   }
   printf("host_selftest ok\n");
   return 0;
