@@ -261,10 +261,14 @@ int gp_pattern_probe(gp_ctx* ctx, const char* uuid, int kind, int pass_begin, in
 int gp_stream_probe(gp_ctx* ctx, const char* uuid, uint32_t which, uint64_t bytes,
                     uint32_t warmup, uint32_t iters, gp_timing* t, uint64_t* checksum);
 /* Run copy / triad once over caller data (parity tests): src arrays are
- * copied to the arena, the kernel runs once, dst is copied back. */
+ * copied to the arena, the kernel runs once, dst is copied back.  bytes is a
+ * multiple of 32; for copy, b is the source and c is ignored. */
 int gp_stream_host(gp_ctx* ctx, const char* uuid, uint32_t which, const void* b, const void* c,
                    float scalar, void* dst, uint64_t bytes);
 
+/* M = N = K = mnk (a multiple of 256; 0 -> 8192) from the counter generator; timed launches,
+ * then `samples` stratified entries checked against an fp64 host reference plus a Freivalds
+ * check of the whole product.  C is fp32 or bf16 per gp_config.gemm_output. */
 int gp_gemm_probe(gp_ctx* ctx, const char* uuid, uint32_t mnk, uint64_t seed, uint32_t warmup,
                   uint32_t iters, uint32_t samples, gp_gemm_result* out);
 /* C (fp32, row-major m x n) = A (bf16 bits, m x k, K-major) * B^T (bf16 bits,
