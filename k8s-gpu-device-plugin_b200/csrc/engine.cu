@@ -348,7 +348,8 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
   const uint32_t iters = ctx->cfg.iters ? ctx->cfg.iters : 10;
   const uint64_t hbm = cfg_hbm_bytes(ctx);
   uint64_t pat = cfg_pattern_bytes(ctx);
-  const bool pat_all = pat == GP_PATTERN_ALL_FREE;
+  const bool pat_all = pat == GP_PATTERN_ALL_FREE && (mask & GP_PROBE_PATTERN);
+  if (pat == GP_PATTERN_ALL_FREE && !pat_all) pat = hbm;  // no pattern probe asked for: nothing to size
   if (pat_all) {
     // whole-memory grading: everything the driver will still give us, minus a margin, in 1 MiB units
     size_t free_b = 0, total_b = 0;
