@@ -200,6 +200,11 @@ int main() {
     CHECK(!qe && quiet.empty() && fb.many_calls == calls && mgr.skippedBusy() >= 1);
     auto [forced, fe2] = mgr.Reprobe("GPU-n0");
     CHECK(!fe2 && forced.size() == 1 && fb.many_calls == calls + 1);
+    // with a reduced engine configured, a busy device gets the small probe instead of none
+    FakeBackend small;
+    mgr.SetReducedBackend(&small, GP_PROBE_COPY | GP_PROBE_PATTERN);
+    auto [red, re3] = mgr.Reprobe("", /*skip_busy=*/true);
+    CHECK(!re3 && red.size() == 2 && small.many_calls == 1 && mgr.reducedProbes() == 1 && fb.many_calls == calls + 2);
     PluginManager bad(MigStrategyNone, {Resource::New("GPU", "gpu")}, [&] { return nodes; }, &fb, &pm, 1);
     CHECK(bad.loadPlugins().value() == "GPU name 'NVIDIA B200' does not match any resource patterns");
   }

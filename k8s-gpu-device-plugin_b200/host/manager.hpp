@@ -226,23 +226,34 @@ class PluginManager {
     { std::lock_guard<std::mutex> g(mu_); for (auto& p : plugins_) p->Stop(); plugins_.clear(); devices_ = DeviceMap(); }
     return loadPlugins();
   }
+  // A second, small-footprint engine (small arrays, few passes) for devices tenants are using: with
+  // it the periodic path gives busy devices the reduced probe instead of leaving them ungraded.
+  void SetReducedBackend(ProbeBackend* reduced, uint32_t reduced_mask) { reduced_be_ = reduced; reduced_mask_ = reduced_mask; }
+
   // re-grade (all, or one uuid) while streams are open: transitions go through Report
-  // skip_busy: leave devices alone (keep their last verdict) while other processes compute on them
+  // skip_busy: devices on which other processes compute are not given the full probe; they get the
+  // reduced one if a reduced backend is set, else keep their last verdict
   std::pair<std::vector<std::shared_ptr<Device>>, Error> Reprobe(const std::string& uuid = "", bool skip_busy = false) {
     std::lock_guard<std::mutex> g(mu_);
-    DeviceMap scope;
+    DeviceMap scope, busy;
     bool known = false;
     for (auto& kv : devices_.m)
       for (auto& dv : kv.second.m)
         if (uuid.empty() || dv.second->GetUUID() == uuid) {
           known = true;
-          if (skip_busy && be_->OtherComputeProcs(dv.second->GetUUID()) > 0) { ++skipped_busy_; continue; }
+          if (skip_busy && be_->OtherComputeProcs(dv.second->GetUUID()) > 0) {
+            if (reduced_be_) { busy.m[kv.first].m[dv.first] = dv.second; ++reduced_probes_; }
+            else ++skipped_busy_;
+            continue;
+          }
           scope.m[kv.first].m[dv.first] = dv.second;
         }
     if (!known) return {{}, "unknown device " + uuid};
-    if (scope.m.empty()) return {{}, std::nullopt};
-    GradeDevices(scope, *be_, mask_, &log_, /*apply_health=*/false);
+    if (scope.m.empty() && busy.m.empty()) return {{}, std::nullopt};
+    if (!scope.m.empty()) GradeDevices(scope, *be_, mask_, &log_, /*apply_health=*/false);
+    if (!busy.m.empty()) GradeDevices(busy, *reduced_be_, reduced_mask_, &log_, /*apply_health=*/false);
     auto all = scope.All();
+    for (auto& d : busy.All()) all.push_back(d);
     for (auto& d : all) {
       metrics_->Update(*d);
       for (auto& p : plugins_) if (p->devices().GetByID(d->ID)) p->Report(d->ID, VerdictHealthy(*d));
@@ -273,6 +284,7 @@ class PluginManager {
   int loads() const { return loads_; }
   int reprobes() const { return reprobes_; }
   int skippedBusy() const { return skipped_busy_; }
+  int reducedProbes() const { return reduced_probes_; }
   int unhealthyAtLoad() const { return unhealthy_at_load_; }
   std::vector<std::string> log() { std::lock_guard<std::mutex> g(mu_); return log_; }
 
@@ -288,7 +300,9 @@ class PluginManager {
   std::vector<std::shared_ptr<NvidiaDevicePlugin>> plugins_;
   std::vector<std::string> log_;
   std::atomic<bool> restart_{false};
-  std::atomic<int> loads_{0}, reprobes_{0}, skipped_busy_{0};
+  std::atomic<int> loads_{0}, reprobes_{0}, skipped_busy_{0}, reduced_probes_{0};
+  ProbeBackend* reduced_be_ = nullptr;
+  uint32_t reduced_mask_ = GP_PROBE_COPY | GP_PROBE_PATTERN;
   int unhealthy_at_load_ = 0;
   std::thread ticker_;
   std::mutex tick_mu_;
