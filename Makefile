@@ -5,7 +5,7 @@ CSRC := $(PKG)/csrc
 LIB := $(PKG)/libgpuprobe.so
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
            -Xcompiler -fPIC,-fvisibility=hidden,-Wall -Xptxas -v
-SRCS := $(CSRC)/engine.cu $(CSRC)/pattern.cu $(CSRC)/stream.cu $(CSRC)/gemm.cu $(CSRC)/p2p.cu $(CSRC)/noalloc.cu $(CSRC)/nvml_lite.cu
+SRCS := $(CSRC)/engine.cu $(CSRC)/pattern.cu $(CSRC)/stream.cu $(CSRC)/gemm.cu $(CSRC)/p2p.cu $(CSRC)/noalloc.cu $(CSRC)/nvml_lite.cu $(CSRC)/arena.cu
 OBJS := $(SRCS:.cu=.o)
 HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/gpuprobe.h
 

@@ -198,6 +198,82 @@ def run_reference(args):
     return 0
 
 
+# ------------------------------------------------------------------ K4 leg ------------------
+LADDER = [64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30]
+NVLINK_GBPS = 900.0  # per direction per GPU
+
+
+def _offdiag(m):
+    n = len(m)
+    return [m[i][j] for i in range(n) for j in range(n) if i != j]
+
+
+def _summ(m):
+    off = _offdiag(m)
+    n = len(m)
+    return {"min": round(min(off), 1), "max": round(max(off), 1), "mean": round(sum(off) / len(off), 1),
+            "frac_of_900": round(sum(off) / len(off) / NVLINK_GBPS, 4), "min_frac_of_900": round(min(off) / NVLINK_GBPS, 4),
+            "flatness_max_over_min": round(max(off) / min(off), 4),
+            "local_mean": round(sum(m[i][i] for i in range(n)) / n, 1)}
+
+
+def fabric_leg(gpuprobe, n, nbytes):
+    """P2P matrices (in-kernel peer loads / stores, 1-factorisation rounds), the copy-engine yardstick in the
+    same schedule, the 64 KiB - 1 GiB ladder, the NCCL all-reduce ladder and the fabric verdict.  Every read
+    is checked against the closed form of what the peer holds, every write / copy where it landed."""
+    out = {}
+    t0 = time.perf_counter()
+    try:
+        with gpuprobe.Probe(keep_arena=1, hbm_bytes=GIB, arena_cap_bytes=9 * GIB, fabric_bytes=nbytes) as p:
+            modes = [("read", gpuprobe.GP_P2P_READ), ("write", gpuprobe.GP_P2P_WRITE),
+                     ("bidir_write", gpuprobe.GP_P2P_BIDIR_WRITE), ("bidir_read", gpuprobe.GP_P2P_BIDIR_READ),
+                     ("copy_engine", gpuprobe.GP_P2P_COPY_ENGINE),
+                     ("copy_engine_bidir", gpuprobe.GP_P2P_COPY_ENGINE_BIDIR)]
+            p2p = {"bytes": nbytes, "n_gpus": n, "unit": UNIT, "peak": NVLINK_GBPS,
+                   "what": "GB/s per direction per ordered pair, best of 3 after a warm-up, CUDA events on the "
+                           "source GPU's stream; pairs scheduled as the n-1 rounds of a 1-factorisation; "
+                           "copy_engine* = cudaMemcpyPeerAsync in the same schedule (the yardstick)"}
+            for name, d in modes:
+                p2p[name] = _summ(p.probe_p2p(n, nbytes, d))
+            m = p.probe_p2p(n, nbytes, gpuprobe.GP_P2P_ALL_AT_ONCE)
+            agg = [m[i][i] for i in range(n)]
+            p2p["all_at_once"] = {"aggregate_ingress_per_gpu": {"min": round(min(agg), 1), "max": round(max(agg), 1),
+                                                                "mean": round(sum(agg) / n, 1)},
+                                  "frac_of_900": round(sum(agg) / n / NVLINK_GBPS, 4)}
+            p2p["write_vs_copy_engine"] = round(p2p["write"]["mean"] / p2p["copy_engine"]["mean"], 4)
+            p2p["read_vs_copy_engine"] = round(p2p["read"]["mean"] / p2p["copy_engine"]["mean"], 4)
+            ladder = {}
+            for name, d in (("read", gpuprobe.GP_P2P_READ), ("write", gpuprobe.GP_P2P_WRITE),
+                            ("copy_engine", gpuprobe.GP_P2P_COPY_ENGINE)):
+                ladder[name] = {str(sz): round(sum(_offdiag(mm)) / (n * (n - 1)), 1)
+                                for sz in LADDER for mm in [p.probe_p2p(n, sz, d)]}
+            p2p["ladder_mean_gbps"] = ladder
+            out["p2p"] = p2p
+            f = p.probe_fabric(n)
+            out["fabric"] = {"healthy": int(f.healthy), "data_ok": int(f.data_ok), "failed_bits": int(f.failed),
+                             "spread": round(f.spread, 4), "worst_pair": [f.worst_src, f.worst_dst],
+                             "worst_gbps": round(f.worst_gbps, 1), "seconds": round(f.duration_s, 3),
+                             "allreduce_busbw_gbps": round(f.allreduce_busbw_gbps, 1)}
+            ar = {"nranks": n, "unit": UNIT, "what": "in-place fp32 sum ncclAllReduce, one communicator per GPU in "
+                  "one process, group launch, max over ranks of the device time; busbw = algbw * 2(n-1)/n"}
+            bus = {}
+            for sz in LADDER + [4 << 30]:
+                try:
+                    a, b = p.probe_allreduce(n, sz, warmup=2, iters=5)
+                    bus[str(sz)] = round(b, 1)
+                except gpuprobe.GpuProbeError as e:
+                    bus[str(sz)] = f"error: {e}"
+                    break
+            ar["busbw_gbps"] = bus
+            good = [v for v in bus.values() if isinstance(v, float)]
+            ar["busbw_peak_gbps"] = max(good) if good else None
+            out["allreduce"] = ar
+    except gpuprobe.GpuProbeError as e:
+        out.setdefault("p2p", {})["error"] = str(e)
+    out.setdefault("p2p", {})["leg_seconds"] = round(time.perf_counter() - t0, 2)
+    return out
+
+
 # ------------------------------------------------------------------ CUDA arm ----------------
 def run_ours(args):
     import gpuprobe
@@ -254,16 +330,22 @@ def run_ours(args):
                     "frac_of_sustained_cublas": (g.tflops_median / sustained) if sustained else None,
                     "frac_of_nominal_2250": g.tflops_best / 2250.0,
                     "max_scaled_err": g.max_scaled_err, "freivalds_err": g.freivalds_err, "tolerance": 1e-3,
-                    "samples": g.samples, "samples_bad": g.samples_bad,
-                    "tensor_pipe_active_pct_ncu": 96.7, "ncu": "profiles/ncu_summary_r01.md"}
+                    "samples": g.samples, "samples_bad": g.samples_bad}
+            try:
+                with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                    gj = json.load(f).get("gemm")
+                if gj:
+                    gemm["ncu"] = gj   # tensor-pipe active %, DRAM bytes per launch, source file (a profiler capture, not this run)
+            except Exception:
+                pass
             # the same problem with C in bf16, which is what the measured cuBLAS bf16 peak (torch.matmul of
-            # bf16 tensors) writes; errors are measured beyond the 2^-8 |ref| rounding of the output
+            # bf16 tensors) writes; the bf16 C must equal RNE(bf16) of the fp32 C of the same plan bit for bit
             with gpuprobe.Probe(keep_arena=1, gemm_output=1) as pg:
                 gb = pg.gemm_probe(dev, mnk=8192, iters=10, warmup=2, samples=4096)
             gemm["bf16_output"] = {"tflops_best": gb.tflops_best, "tflops_median": gb.tflops_median,
                                    "frac": gb.tflops_best / burst, "frac_of_nominal_2250": gb.tflops_best / 2250.0,
                                    "max_scaled_err": gb.max_scaled_err, "freivalds_err": gb.freivalds_err,
-                                   "samples_bad": gb.samples_bad}
+                                   "samples_bad": gb.samples_bad, "bf16_mismatches_vs_rne_fp32": gb.bf16_mismatches}
         except gpuprobe.GpuProbeError as e:
             gemm = {"error": str(e)} if gemm is None else dict(gemm, bf16_output={"error": str(e)})
 
@@ -301,42 +383,60 @@ def run_ours(args):
 
     wall_max, dev_ms_max = max_over_ranks(dist, [wall, dev_ms], "cuda")
 
-    e2e = None
-    if args.no_e2e:
-        probe.close()
-        p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
-    else:
-        # ---- e2e: the call the plugin makes (gp_probe_device), cold arena, results to host -----
-        probe.close()
-        e2e_calls = max(1, min(args.steps, args.e2e_calls))
-        mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_TRIAD | gpuprobe.GP_PROBE_PATTERN
-        p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
-        p2.probe_device(dev, mask)  # warm-up call (context, module load)
-        p2.kernel_stats(dev, reset=True)
+    e2e, e2e_cold = None, None
+    probe.close()
+    mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_TRIAD | gpuprobe.GP_PROBE_PATTERN
+
+    def e2e_leg(p, calls, what):
+        """`calls` back-to-back gp_probe_device calls on every rank at once, host clock, max over ranks."""
+        p.kernel_stats(dev, reset=True)
         barrier()
         t0 = time.perf_counter()
-        last = None
-        for _ in range(e2e_calls):
-            last = p2.probe_device(dev, mask)   # malloc arena, generate, warm up, time, verify, D2H, free
-            if not last.healthy:
-                raise SystemExit(f"e2e: gp_probe_device verdict unhealthy, failed_mask={last.failed_mask}")
+        res = []
+        for _ in range(calls):
+            r = p.probe_device(dev, mask)   # generate, warm up, time, 64+2 fill/verify passes, verify, results D2H
+            if not r.healthy:
+                raise SystemExit(f"e2e: gp_probe_device verdict unhealthy, failed_mask={r.failed_mask}")
+            res.append(r)
         barrier()
-        e2e_wall = time.perf_counter() - t0
-        st2 = p2.kernel_stats(dev)
-        e2e_bytes = sum(st2[i].algo_bytes for i in (gpuprobe.GP_K_COPY, gpuprobe.GP_K_TRIAD,
-                                                    gpuprobe.GP_K_FILL, gpuprobe.GP_K_VERIFY))
-        e2e_launches = sum(int(st2[i].launches) for i in range(7))
-        e2e_wall = max_over_ranks(dist, [e2e_wall], "cuda")[0]
-        d2h = ctypes.sizeof(gpuprobe.DeviceResult) + last.pattern_passes * 48 + 48 + 8
-        e2e = {"value": e2e_bytes * n_gpus / e2e_wall / 1e9, "unit": UNIT,
-               "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h,
-               "calls": e2e_calls, "seconds_per_call": e2e_wall / e2e_calls,
-               "launches_per_call": e2e_launches // e2e_calls,
-               "what": "gp_probe_device(uuid, COPY|TRIAD|PATTERN) through the C ABI with a cold arena: "
-                       "cudaMalloc, operand generation, warm-up + timed launches, 64+2 fill/verify "
-                       "passes, verification, results copied to the caller's host struct, cudaFree. "
-                       "The probe takes no bulk host input by construction (patterns are generated "
-                       "on the device it grades), so h2d is 0 and d2h is the result bytes."}
+        w = time.perf_counter() - t0
+        st2 = p.kernel_stats(dev)
+        nb = sum(st2[i].algo_bytes for i in (gpuprobe.GP_K_COPY, gpuprobe.GP_K_TRIAD,
+                                             gpuprobe.GP_K_FILL, gpuprobe.GP_K_VERIFY))
+        launches = sum(int(st2[i].launches) for i in range(7))
+        mean = lambda f: sum(getattr(r, f) for r in res) / len(res)
+        w, a_s, f_s, k_s = max_over_ranks(dist, [w, mean("alloc_s"), mean("free_s"), mean("kernels_s")], "cuda")
+        d2h = ctypes.sizeof(gpuprobe.DeviceResult) + res[-1].pattern_passes * 48 + 48 + 8
+        return {"value": nb * n_gpus / w / 1e9, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": d2h,
+                "calls": calls, "seconds_per_call": w / calls, "launches_per_call": launches // calls,
+                "alloc_s_per_call": a_s, "free_s_per_call": f_s, "kernels_s_per_call": k_s,
+                "arena_bytes": int(res[-1].arena_bytes),
+                "arena_backend": {1: "vmm", 2: "cudaMalloc"}.get(int(res[-1].arena_backend), "?"),
+                "arena_reused": int(res[-1].arena_reused), "what": what}
+
+    if args.no_e2e:
+        p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
+    else:
+        e2e_calls = max(1, min(args.steps, args.e2e_calls))
+        # ---- e2e: the call the plugin makes on every periodic re-probe of an idle device.  The arena
+        # stays mapped while the device is unassigned (keep_arena = 1) and goes back to the pods in
+        # Allocate (gp_trim_device), so the steady-state call allocates nothing.
+        pk = gpuprobe.Probe(keep_arena=1, hbm_bytes=nbytes, stream_variant=variant)
+        pk.probe_device(dev, mask)  # first call of the process: context, module load, arena
+        e2e = e2e_leg(pk, e2e_calls,
+                      "gp_probe_device(uuid, COPY|TRIAD|PATTERN) through the C ABI, arena kept between calls "
+                      "(keep_arena = 1: the periodic re-probe of an idle device; gp_trim_device returns the "
+                      "memory in Allocate): operand generation, warm-up + timed launches, 64+2 fill/verify "
+                      "passes, verification, results copied to the caller's host struct.  The probe takes no "
+                      "bulk host input by construction (patterns are generated on the device it grades), so "
+                      "h2d is 0 and d2h is the result bytes.")
+        pk.close()
+        # ---- the same call with a cold arena every time (keep_arena = 0: the start-up grade); alloc_s and
+        # free_s say what the allocator costs when all N processes hit the driver at once
+        p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
+        p2.probe_device(dev, mask)
+        e2e_cold = e2e_leg(p2, e2e_calls, "same call with keep_arena = 0: the arena is mapped at entry and "
+                                          "released before return on every call")
 
     # ---- the literal host-buffer reading of e2e, for the record: grade 1 GiB that lives in pinned HOST
     # memory (H2D copy + verify + 48-byte result back).  This measures PCIe, not the device, and is not
@@ -399,6 +499,14 @@ def run_ours(args):
                     sweep = {"error": str(e2)}
             p3.close()
         host_barrier()
+    # ---- K4: the only cross-GPU paths, rank 0 drives all N GPUs from one process (the plugin's shape)
+    fabric = None
+    if n_gpus >= 2 and not args.no_fabric:
+        p2.trim()
+        host_barrier()
+        if rank == 0:
+            fabric = fabric_leg(gpuprobe, n_gpus, args.fabric_bytes)
+        host_barrier()
     host_barrier()
     p2.close()
 
@@ -459,6 +567,10 @@ def run_ours(args):
         "e2e": e2e,
         "gpu_launches": gpu_launches,
     }
+    if e2e_cold is not None:
+        line["e2e_cold"] = e2e_cold
+    if fabric is not None:
+        line.update(fabric)
     if sweep is not None:
         line["sweep"] = sweep
     if gemm is not None:
@@ -491,6 +603,8 @@ def main():
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the e2e leg")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-fabric", action="store_true", help="skip the P2P / all-reduce legs at --gpus >= 2")
+    ap.add_argument("--fabric-bytes", type=int, default=GIB, help="bytes per transfer of the headline P2P matrices")
     args = ap.parse_args()
     if args.steps < 1:
         raise SystemExit("--steps must be >= 1")

@@ -43,7 +43,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define GP_ABI_VERSION 1u
+#define GP_ABI_VERSION 2u
 
 typedef struct gp_ctx gp_ctx;
 
@@ -56,7 +56,10 @@ typedef enum gp_error {
   GP_ERR_NOMEM = -5,        /* arena allocation failed / request exceeds arena cap */
   GP_ERR_UNSUPPORTED = -6,  /* device is not sm_100 (tcgen05/TMA paths) or no peer access */
   GP_ERR_STRUCT_SIZE = -7,  /* struct_size mismatch between caller and library */
-  GP_ERR_TOO_LARGE = -8     /* request exceeds a fixed compile-time limit */
+  GP_ERR_TOO_LARGE = -8,    /* request exceeds a fixed compile-time limit */
+  GP_ERR_DEVICE_LOST = -9   /* a sticky CUDA fault (illegal address, uncorrectable ECC, Xid ...) has killed this
+                             * process's context on the device: every later call on it returns this code until
+                             * gp_device_reset, or until the device is graded again from a fresh process */
 } gp_error;
 
 /* pattern kinds — SURVEY.md §8(c) */
@@ -97,6 +100,28 @@ enum {
 
 #define GP_PATTERN_ALL_FREE UINT64_MAX
 
+/* GEMM kernels (gp_config.gemm_variant) */
+enum {
+  GP_GEMM_AUTO = 0,           /* 2-CTA pairs; 256 x 512 tiles when N % 512 == 0, else 256 x 256 */
+  GP_GEMM_1CTA_128x256 = 1,   /* cta_group::1, one CTA per 128 x 256 tile */
+  GP_GEMM_2CTA_256x256 = 2,   /* cta_group::2, 256 x 256 tile per pair, accumulator double-buffered */
+  GP_GEMM_2CTA_256x512 = 3    /* as AUTO */
+};
+/* test-only fault injection (gp_config.test_fault); nothing here touches the hardware abnormally */
+enum {
+  GP_TEST_FAULT_GEMM_SKIP_TILE = 1u << 0, /* after the launches, one 256 x 256 tile of C is put back to its NaN fill */
+  GP_TEST_FAULT_GEMM_FLIP_BIT = 1u << 1   /* one low mantissa bit of one element of the timed C is flipped */
+};
+
+/* arena backends (gp_config.arena_backend) */
+enum {
+  GP_ARENA_AUTO = 0,   /* VMM when the driver offers it, else cudaMalloc */
+  GP_ARENA_VMM = 1,    /* one reserved virtual range per device, physical chunks (cuMemCreate) mapped as the
+                        * arena grows: growing never moves or re-allocates what is already mapped */
+  GP_ARENA_MALLOC = 2  /* one cudaMalloc per size change (round-1 behaviour) */
+};
+#define GP_FABRIC_MAX_GPUS 16
+
 typedef struct gp_config {
   uint32_t struct_size;    /* = sizeof(gp_config) */
   uint32_t abi_version;    /* = GP_ABI_VERSION */
@@ -116,7 +141,20 @@ typedef struct gp_config {
   double min_copy_gbps;    /* health floors; 0 -> not enforced */
   double min_triad_gbps;
   double min_gemm_tflops;
-  double gemm_tol;         /* |c-ref| <= gemm_tol * sum_k|a||b| (+ 2^-8 |ref| for bf16 output); 0 -> 1e-3 */
+  double gemm_tol;         /* |c-ref| <= gemm_tol * sum_k|a||b| against the fp64 host reference; 0 -> 1e-3.
+                            * A bf16 C is compared, bit for bit, with RNE(bf16) of the fp32 C of the same problem. */
+  /* ---- ABI 2 ---- */
+  double min_p2p_gbps;     /* fabric floors for gp_probe_fabric; 0 -> not enforced.  Worst off-diagonal pair, GB/s */
+  double max_p2p_spread;   /* largest allowed max/min over the off-diagonal pairs (a flat matrix is the NVSwitch
+                            * health signal); 0 -> not enforced */
+  double min_allreduce_busbw_gbps;
+  uint64_t fabric_bytes;   /* bytes per transfer of gp_probe_fabric; 0 -> 1 GiB */
+  uint32_t arena_backend;  /* GP_ARENA_* */
+  uint32_t sm_limit;       /* size every persistent grid as if the device had this many SMs (a MIG slice exposes
+                            * 1/7 .. 4/7 of them; tests use this to run the launchers at slice scale); 0 -> all */
+  uint32_t gemm_variant;   /* GP_GEMM_*: which tcgen05 kernel the GEMM probe launches */
+  uint32_t test_fault;     /* GP_TEST_FAULT_* bits, tests only: make a check see what a broken GPU would produce */
+  uint32_t reserved2[2];
 } gp_config;
 
 /* One verify pass — SURVEY.md §8(c).  All sums are mod 2^64. */
@@ -148,8 +186,10 @@ typedef struct gp_gemm_result {
   uint32_t samples;
   uint32_t samples_bad;    /* samples exceeding gemm_tol */
   uint64_t c_checksum;     /* XOR of C's bit patterns folded to 64 bit */
-  uint32_t output_bf16;    /* 1 if C was bf16: errors are then measured beyond the 2^-8 |ref| output rounding */
+  uint32_t output_bf16;    /* 1 if the timed C was bf16.  The fp64 checks then run on the fp32 C of the same launch
+                            * plan (one extra untimed launch) and the bf16 C must equal RNE(bf16) of it bit for bit */
   uint32_t reserved;
+  uint64_t bf16_mismatches;/* elements of the bf16 C that differ from RNE(fp32 C); counted into samples_bad */
 } gp_gemm_result;
 
 typedef struct gp_device_result {
@@ -181,7 +221,36 @@ typedef struct gp_device_result {
   uint64_t first_bad_index, first_bad_xor;
   uint64_t pattern_digest;  /* checksum of checksums: SUM over passes of (sum ^ rotl(xor,1) ^ rotl(wsum,2)) * (pass_no+1) */
   gp_gemm_result gemm;
+  /* ---- ABI 2: where duration_s went (host steady_clock) ---- */
+  double alloc_s;           /* growing the arena inside this call (0 when the kept arena was large enough) */
+  double free_s;            /* releasing it before return (keep_arena = 0 only) */
+  double kernels_s;         /* duration_s - alloc_s - free_s: generation, warm-up, timed launches, checks, copies */
+  uint64_t arena_bytes;     /* device memory the call ran in */
+  uint32_t arena_reused;    /* 1 if the arena was already there on entry (periodic re-probe of an idle device) */
+  uint32_t arena_backend;   /* GP_ARENA_VMM or GP_ARENA_MALLOC actually used */
 } gp_device_result;
+
+/* Verdict on the GPU-to-GPU fabric (K4 of SURVEY.md §8): the P2P matrices, their spread, the worst pair and the
+ * NCCL all-reduce bus bandwidth, against the floors of gp_config.  Row = source GPU, n*n entries used. */
+typedef struct gp_fabric_result {
+  uint32_t struct_size;
+  uint32_t ngpus;
+  uint64_t bytes;                /* per transfer */
+  double read_gbps[GP_FABRIC_MAX_GPUS * GP_FABRIC_MAX_GPUS];   /* kernel on row GPU loads from column GPU */
+  double write_gbps[GP_FABRIC_MAX_GPUS * GP_FABRIC_MAX_GPUS];  /* kernel on row GPU stores to column GPU  */
+  double read_min, read_max, read_mean;     /* off-diagonal */
+  double write_min, write_max, write_mean;
+  double spread;                 /* max over {read, write} of max/min off-diagonal; 1.0 = perfectly flat */
+  int32_t worst_src, worst_dst;  /* the slowest ordered pair over both matrices, -1 if ngpus < 2 */
+  double worst_gbps;
+  double allreduce_algbw_gbps, allreduce_busbw_gbps;  /* 0 if the all-reduce was not run (ngpus < 2 or no NCCL) */
+  int32_t allreduce_error;       /* gp_error of the all-reduce leg (NCCL missing is reported here, not fatal) */
+  uint32_t data_ok;              /* 1 iff every peer read returned the bytes the peer holds and every peer write landed */
+  uint32_t failed;               /* bit 0: below min_p2p_gbps, 1: spread above max_p2p_spread, 2: all-reduce below its
+                                  * floor, 3: data mismatch */
+  int32_t healthy;               /* 1 iff failed == 0 */
+  double duration_s;
+} gp_fabric_result;
 
 typedef struct gp_kernel_stat {
   uint64_t launches;
@@ -197,11 +266,22 @@ int gp_init(const gp_config* cfg, gp_ctx** out);
 void gp_shutdown(gp_ctx* ctx);
 /* Free every per-device arena (pods need the memory once grading is done). */
 int gp_trim(gp_ctx* ctx);
+/* Free ONE device's arena.  With keep_arena = 1 the arena of an idle device stays mapped between periodic
+ * re-probes (no allocation inside the probe call); the plugin hands the memory back the moment kubelet
+ * assigns the device: call this from Allocate (plugin/plugin.go:210-225), before the pod starts. */
+int gp_trim_device(gp_ctx* ctx, const char* uuid);
+/* Recover a device that returned GP_ERR_DEVICE_LOST without restarting the process: drops every handle the
+ * library holds on it and calls cudaDeviceReset.  This destroys the device's primary context for the WHOLE
+ * process, so it is only for hosts where nothing else uses CUDA on that device (the Go plugin is one).  The
+ * reference's own recovery is a full plugin restart (plugin/plugin.go:107-129). */
+int gp_device_reset(gp_ctx* ctx, const char* uuid);
+/* 1 if a sticky fault has been seen on the device since the last reset, else 0; negative gp_error on bad arguments. */
+int gp_device_poisoned(gp_ctx* ctx, const char* uuid);
 uint32_t gp_abi_version(void);
 /* sizeof() of the POD structs as this library was compiled, so a binding in
  * another language can check its own layout: which = 0 gp_config,
  * 1 gp_pattern_result, 2 gp_timing, 3 gp_gemm_result, 4 gp_device_result,
- * 5 gp_kernel_stat, 6 gp_nvml_info; 0 for anything else. */
+ * 5 gp_kernel_stat, 6 gp_nvml_info, 7 gp_fabric_result; 0 for anything else. */
 size_t gp_sizeof(int which);
 const char* gp_strerror(int err);
 /* Thread-local text of the last failure on this thread ("" if none). */
@@ -308,6 +388,13 @@ int gp_kernel_stats(gp_ctx* ctx, const char* uuid, gp_kernel_stat* out /*[GP_K_C
  *   - all calls on a device share the one array: two calls whose kernels overlap
  *     on the GPU (different streams, or different threads) race and return
  *     garbage — serialise them; calls on one stream are safe;
+ *   - d_words must be 32-byte aligned (the kernels load 256 bits at a time) and d_result
+ *     8-byte aligned, else GP_ERR_INVALID: grading a sub-range of a buffer is fine as long as
+ *     it starts on a 32-byte boundary;
+ *   - the address looked up on the first call is cached per device ordinal for the life of the
+ *     process.  cudaDeviceReset destroys the array with the rest of the context: gp_device_reset
+ *     drops the cached address, but after a reset done behind the library's back this entry
+ *     point must not be called again on that device;
  *   - calls cudaSetDevice(device_ordinal) on the calling thread. */
 #define GP_NOALLOC_MAX_WORDS (1ull << 35) /* 256 GiB of graded memory per call */
 int gp_pattern_verify_noalloc(int device_ordinal, const uint64_t* d_words, uint64_t nwords, int kind,
@@ -315,6 +402,11 @@ int gp_pattern_verify_noalloc(int device_ordinal, const uint64_t* d_words, uint6
 
 /* Test-only fault injection: flip `bit` of arena word `word_index`. */
 int gp_inject_bitflip(gp_ctx* ctx, const char* uuid, uint64_t word_index, int bit);
+/* Test-only: behave as if a CUDA call on the device had just failed with `cuda_error` (a cudaError_t value).
+ * Nothing is launched and the GPU is not touched; the error goes through the library's own classification, so
+ * a sticky code (e.g. 700 cudaErrorIllegalAddress, 214 cudaErrorECCUncorrectable) marks the device lost exactly
+ * as the real fault would.  Returns the gp_error the failing call would have returned. */
+int gp_inject_cuda_error(gp_ctx* ctx, const char* uuid, int cuda_error);
 
 /* ---- multi-GPU (the only cross-device paths) ---------------------------- */
 
@@ -324,8 +416,21 @@ int gp_inject_bitflip(gp_ctx* ctx, const char* uuid, uint64_t word_index, int bi
  * dir 3 = all pairs at once (switch saturation): every GPU reads `bytes` from
  * each peer concurrently; row i = GPU i's aggregate ingress / (n-1), diagonal =
  * the aggregate.  dir 4 = bidirectional read (both GPUs of a pair read from each
- * other at once). */
+ * other at once).  dir 5 / 6 = the copy-engine yardstick: cudaMemcpyPeerAsync
+ * src -> dst, one direction / both directions at once, same schedule and timing
+ * as the kernels so the two can be read side by side.
+ * Every read mode folds what it loaded (sum and xor of the u64 words) and the
+ * host compares that with the closed form of the address pattern the peer
+ * holds; every write mode checks what landed.  A mismatch is GP_ERR_CUDA. */
+enum {
+  GP_P2P_READ = 0, GP_P2P_WRITE = 1, GP_P2P_BIDIR_WRITE = 2, GP_P2P_ALL_AT_ONCE = 3,
+  GP_P2P_BIDIR_READ = 4, GP_P2P_COPY_ENGINE = 5, GP_P2P_COPY_ENGINE_BIDIR = 6
+};
 int gp_probe_p2p(gp_ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps);
+/* Read + write matrices at gp_config.fabric_bytes, then the all-reduce, graded against the fabric floors.
+ * Called once after the single-GPU grade (plugin/manager.go:156-174); its matrix is what
+ * GetPreferredAllocation ranks by (plugin/plugin.go:192-207, :256-282). */
+int gp_probe_fabric(gp_ctx* ctx, int ngpus, gp_fabric_result* out);
 /* In-place fp32 sum ncclAllReduce over the first nranks devices. */
 int gp_probe_allreduce(gp_ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters,
                        double* algbw_gbps, double* busbw_gbps);

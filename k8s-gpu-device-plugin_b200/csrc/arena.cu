@@ -1,0 +1,250 @@
+// arena.cu — the per-device arena every probe carves its arrays from.
+//
+// No reference counterpart (the reference never allocates device memory).  Two backends:
+//
+//   VMM (default): one virtual range per device is reserved on first use (cuMemAddressReserve; virtual
+//   space is free) and physical chunks (cuMemCreate, 1 GiB each plus one tail chunk) are mapped from
+//   its base upwards as the arena grows.  Growing never moves what is already mapped, so a kept arena
+//   (keep_arena = 1, the periodic re-probe of an idle device) costs nothing inside the probe call and
+//   a larger request only maps the difference.  gp_trim / gp_trim_device unmap and release the
+//   physical memory (pods get it back) but keep the reservation.
+//
+//   cudaMalloc: one allocation per size change, as in round 1 (kept for devices / drivers without
+//   VMM support and as the A/B baseline; gp_config.arena_backend selects).
+//
+// Measured reason (SCALE_r01): cudaMalloc + cudaFree of 48 GiB inside every
+// gp_probe_device call cost ~55 ms alone and ~225 ms when eight processes did it at once (the
+// driver serialises memory management across processes); Device::alloc_s / free_s now report it.
+#include <cuda.h>
+
+#include <chrono>
+
+#include "engine.h"
+
+namespace gp {
+
+namespace {
+
+struct VmmApi {
+  bool ok = false;
+  CUresult (*AddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+  CUresult (*AddressFree)(CUdeviceptr, size_t) = nullptr;
+  CUresult (*Create)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long) = nullptr;
+  CUresult (*Release)(CUmemGenericAllocationHandle) = nullptr;
+  CUresult (*Map)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+  CUresult (*Unmap)(CUdeviceptr, size_t) = nullptr;
+  CUresult (*SetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t) = nullptr;
+  CUresult (*GetGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags) = nullptr;
+};
+
+template <class F>
+bool entry(const char* name, F* out) {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) {
+    (void)cudaGetLastError();
+    return false;
+  }
+  *out = reinterpret_cast<F>(p);
+  return true;
+}
+
+const VmmApi* vmm_api() {
+  static VmmApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    api.ok = entry("cuMemAddressReserve", &api.AddressReserve) && entry("cuMemAddressFree", &api.AddressFree) &&
+             entry("cuMemCreate", &api.Create) && entry("cuMemRelease", &api.Release) &&
+             entry("cuMemMap", &api.Map) && entry("cuMemUnmap", &api.Unmap) &&
+             entry("cuMemSetAccess", &api.SetAccess) &&
+             entry("cuMemGetAllocationGranularity", &api.GetGranularity);
+  });
+  return &api;
+}
+
+constexpr size_t kChunkBytes = 1ull << 30;
+
+int cu_fail(CUresult r, const char* what) {
+  set_error("%s failed: CUresult %d", what, (int)r);
+  return r == CUDA_ERROR_OUT_OF_MEMORY ? GP_ERR_NOMEM : GP_ERR_CUDA;
+}
+
+bool device_supports_vmm(int ordinal) {
+  CUresult (*GetDev)(CUdevice*, int) = nullptr;
+  CUresult (*GetAttr)(int*, CUdevice_attribute, CUdevice) = nullptr;
+  if (!entry("cuDeviceGet", &GetDev) || !entry("cuDeviceGetAttribute", &GetAttr)) return false;
+  CUdevice dev;
+  int vmm = 0;
+  if (GetDev(&dev, ordinal) != CUDA_SUCCESS) return false;
+  if (GetAttr(&vmm, CU_DEVICE_ATTRIBUTE_VIRTUAL_MEMORY_MANAGEMENT_SUPPORTED, dev) != CUDA_SUCCESS) return false;
+  return vmm != 0;
+}
+
+CUmemAccessDesc access_for(int ordinal) {
+  CUmemAccessDesc a{};
+  a.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  a.location.id = ordinal;
+  a.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  return a;
+}
+
+// unmap + release everything mapped above `keep_bytes` (a chunk boundary); VMM backend only
+void vmm_shrink(Device* d, size_t keep_bytes) {
+  const VmmApi* api = vmm_api();
+  size_t off = d->arena_bytes;
+  while (!d->chunks.empty() && off > keep_bytes) {
+    const Device::Chunk c = d->chunks.back();
+    off -= c.bytes;
+    api->Unmap((CUdeviceptr)(d->va_base + off), c.bytes);
+    api->Release((CUmemGenericAllocationHandle)c.handle);
+    d->chunks.pop_back();
+  }
+  d->arena_bytes = off;
+  if (off == 0) { d->arena = nullptr; d->peer_mask = 0; }
+}
+
+int vmm_grow(Ctx* ctx, Device* d, size_t bytes) {
+  (void)ctx;
+  const VmmApi* api = vmm_api();
+  CUmemAllocationProp prop{};
+  prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  prop.location.id = d->ordinal;
+  size_t gran = 0;
+  CUresult r = api->GetGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED);
+  if (r != CUDA_SUCCESS || gran == 0) return cu_fail(r, "cuMemGetAllocationGranularity");
+  if (!d->va_base) {
+    // everything the device could ever hold, rounded up: virtual space costs nothing
+    size_t va = ((size_t)d->total_mem + 2 * kChunkBytes - 1) / kChunkBytes * kChunkBytes;
+    CUdeviceptr base = 0;
+    r = api->AddressReserve(&base, va, kChunkBytes, 0, 0);
+    if (r != CUDA_SUCCESS) return cu_fail(r, "cuMemAddressReserve");
+    d->va_base = (unsigned long long)base;
+    d->va_bytes = va;
+  }
+  if (bytes > d->va_bytes) { set_error("arena request %zu exceeds the device's address range %zu", bytes, d->va_bytes); return GP_ERR_NOMEM; }
+  const size_t old_bytes = d->arena_bytes;
+  size_t off = old_bytes;
+  while (off < bytes) {
+    size_t want = std::min(kChunkBytes, bytes - off);
+    want = (want + gran - 1) / gran * gran;
+    CUmemGenericAllocationHandle h = 0;
+    r = api->Create(&h, want, &prop, 0);
+    if (r != CUDA_SUCCESS) { d->arena_bytes = off; vmm_shrink(d, old_bytes); return cu_fail(r, "cuMemCreate"); }
+    r = api->Map((CUdeviceptr)(d->va_base + off), want, 0, h, 0);
+    if (r != CUDA_SUCCESS) { api->Release(h); d->arena_bytes = off; vmm_shrink(d, old_bytes); return cu_fail(r, "cuMemMap"); }
+    d->chunks.push_back({(unsigned long long)h, want});
+    off += want;
+  }
+  // access for the owner and for every peer that already sees the lower part
+  std::vector<CUmemAccessDesc> acc;
+  acc.push_back(access_for(d->ordinal));
+  for (int i = 0; i < 64; ++i)
+    if (i != d->ordinal && (d->peer_mask >> i & 1)) acc.push_back(access_for(i));
+  r = api->SetAccess((CUdeviceptr)(d->va_base + old_bytes), off - old_bytes, acc.data(), acc.size());
+  if (r != CUDA_SUCCESS) { d->arena_bytes = off; vmm_shrink(d, old_bytes); return cu_fail(r, "cuMemSetAccess"); }
+  d->arena = reinterpret_cast<uint8_t*>(d->va_base);
+  d->arena_bytes = off;
+  d->arena_is_vmm = true;
+  return GP_OK;
+}
+
+bool want_vmm(const Ctx* ctx, const Device* d) {
+  if (ctx->cfg.arena_backend == GP_ARENA_MALLOC) return false;
+  static bool supported[64] = {};
+  static bool known[64] = {};
+  if (!vmm_api()->ok || d->ordinal < 0 || d->ordinal >= 64) return false;
+  if (!known[d->ordinal]) { supported[d->ordinal] = device_supports_vmm(d->ordinal); known[d->ordinal] = true; }
+  return supported[d->ordinal];
+}
+
+struct Stopwatch {
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  double seconds() const { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
+}  // namespace
+
+uint64_t cfg_arena_cap(const Ctx* c) {
+  const uint64_t hbm = c->cfg.hbm_bytes ? c->cfg.hbm_bytes : (16ull << 30);
+  return c->cfg.arena_cap_bytes ? c->cfg.arena_cap_bytes : 5 * hbm + (1ull << 30);
+}
+
+void free_arena(Device* d) {
+  if (!d->arena) { d->arena_bytes = 0; d->triad_operands_bytes = 0; return; }
+  Stopwatch sw;
+  cudaSetDevice(d->ordinal);
+  if (d->arena_is_vmm) {
+    vmm_shrink(d, 0);
+  } else {
+    cudaFree(d->arena);
+  }
+  d->arena = nullptr;
+  d->arena_bytes = 0;
+  d->peer_mask = 0;
+  d->triad_operands_bytes = 0;
+  d->free_s += sw.seconds();
+}
+
+void release_arena_va(Device* d) {
+  free_arena(d);
+  if (d->va_base && vmm_api()->ok) vmm_api()->AddressFree((CUdeviceptr)d->va_base, d->va_bytes);
+  d->va_base = 0;
+  d->va_bytes = 0;
+  d->arena_is_vmm = false;
+}
+
+int ensure_arena(Ctx* ctx, Device* d, size_t bytes, bool ignore_cap) {
+  if (bytes <= d->arena_bytes) return GP_OK;
+  if (!ignore_cap && bytes > cfg_arena_cap(ctx)) {
+    set_error("arena request %zu exceeds cap %llu", bytes, (unsigned long long)cfg_arena_cap(ctx));
+    return GP_ERR_NOMEM;
+  }
+  Stopwatch sw;
+  const bool vmm = want_vmm(ctx, d);
+  if (d->arena && d->arena_is_vmm != vmm) free_arena(d);
+  if (!vmm) free_arena(d);  // cudaMalloc cannot grow in place
+  size_t free_b = 0, total_b = 0;
+  cudaError_t e = cudaMemGetInfo(&free_b, &total_b);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemGetInfo", nullptr);
+  int rc = GP_OK;
+  if (vmm) {
+    if (bytes - d->arena_bytes > free_b) {
+      set_error("arena request %zu exceeds free device memory %zu (+%zu already mapped)", bytes, free_b, d->arena_bytes);
+      rc = GP_ERR_NOMEM;
+    } else {
+      rc = vmm_grow(ctx, d, bytes);
+    }
+  } else {
+    if (bytes > free_b) {
+      set_error("arena request %zu exceeds free device memory %zu", bytes, free_b);
+      rc = GP_ERR_NOMEM;
+    } else {
+      void* p = nullptr;
+      e = cudaMalloc(&p, bytes);
+      if (e != cudaSuccess) rc = cuda_fail(e, "cudaMalloc(arena)", nullptr);
+      else {
+        d->arena = reinterpret_cast<uint8_t*>(p);
+        d->arena_bytes = bytes;
+        d->arena_is_vmm = false;
+      }
+    }
+  }
+  d->alloc_s += sw.seconds();
+  return rc;
+}
+
+int arena_grant_peers(Device* d, unsigned long long ordinal_mask) {
+  if (!d->arena || !d->arena_is_vmm) return GP_OK;
+  const unsigned long long add = ordinal_mask & ~d->peer_mask & ~(1ull << d->ordinal);
+  if (!add) return GP_OK;
+  std::vector<CUmemAccessDesc> acc;
+  for (int i = 0; i < 64; ++i)
+    if (add >> i & 1) acc.push_back(access_for(i));
+  const CUresult r = vmm_api()->SetAccess((CUdeviceptr)d->va_base, d->arena_bytes, acc.data(), acc.size());
+  if (r != CUDA_SUCCESS) return cu_fail(r, "cuMemSetAccess(peers)");
+  d->peer_mask |= add;
+  return GP_OK;
+}
+
+}  // namespace gp

@@ -9,6 +9,7 @@
 // consume.  There is deliberately no CPU fallback in this file: if CUDA is
 // unavailable every call returns GP_ERR_CUDA / GP_ERR_NO_DEVICE.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
@@ -30,9 +31,40 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+// The errors after which the context is gone: the runtime returns them again from every later call on
+// the device, whatever the call (CUDA runtime API, "sticky" errors), so the only honest verdict is
+// "lost" and the only recovery a reset or a fresh process.
+bool cuda_error_is_sticky(cudaError_t e) {
+  switch (e) {
+    case cudaErrorIllegalAddress: case cudaErrorLaunchFailure: case cudaErrorHardwareStackError:
+    case cudaErrorIllegalInstruction: case cudaErrorMisalignedAddress: case cudaErrorInvalidAddressSpace:
+    case cudaErrorInvalidPc: case cudaErrorECCUncorrectable: case cudaErrorLaunchTimeout:
+    case cudaErrorAssert: case cudaErrorNvlinkUncorrectable: case cudaErrorTensorMemoryLeak:
+    case cudaErrorMpsClientTerminated: case cudaErrorExternalDevice: case cudaErrorDevicesUnavailable:
+    case cudaErrorUnknown:
+      return true;
+    default:
+      return false;
+  }
+}
+
+static std::atomic<unsigned long long> g_poisoned{0};
+unsigned long long poisoned_ordinals() { return g_poisoned.load(std::memory_order_acquire); }
+void clear_poisoned_ordinal(int ordinal) {
+  if (ordinal >= 0 && ordinal < 64) g_poisoned.fetch_and(~(1ull << ordinal), std::memory_order_acq_rel);
+}
+
 int cuda_fail(cudaError_t e, const char* what, int64_t* detail) {
-  set_error("%s: %s (%d)", what, cudaGetErrorString(e), (int)e);
   if (detail) *detail = (int64_t)e;
+  if (cuda_error_is_sticky(e)) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) == cudaSuccess && cur >= 0 && cur < 64)
+      g_poisoned.fetch_or(1ull << cur, std::memory_order_acq_rel);
+    set_error("%s: %s (%d) - sticky fault, the context on device %d is lost", what, cudaGetErrorString(e), (int)e, cur);
+    (void)cudaGetLastError();
+    return GP_ERR_DEVICE_LOST;
+  }
+  set_error("%s: %s (%d)", what, cudaGetErrorString(e), (int)e);
   (void)cudaGetLastError();
   return e == cudaErrorMemoryAllocation ? GP_ERR_NOMEM : GP_ERR_CUDA;
 }
@@ -83,6 +115,7 @@ int resolve_variant(const Ctx* ctx) {
 }
 
 static void device_release(Device* d) {
+  release_arena_va(d);
   if (d->scratch) cudaFree(d->scratch);
   if (d->h_results) cudaFreeHost(d->h_results);
   for (auto& ev : d->events)
@@ -115,6 +148,12 @@ static int device_prepare_once(Device* d) {
 
 int device_prepare(Ctx* ctx, Device* d) {
   (void)ctx;
+  if (poisoned_ordinals() >> d->ordinal & 1) d->poisoned = true;
+  if (d->poisoned) {
+    set_error("device %d (%s) was lost to a sticky CUDA fault earlier in this process (cudaError %d): "
+              "gp_device_reset it or grade it from a fresh process", d->ordinal, d->uuid, d->poison_code);
+    return GP_ERR_DEVICE_LOST;
+  }
   CU_OR_RETURN(cudaSetDevice(d->ordinal), nullptr);
   if (d->ready) return GP_OK;
   const int rc = device_prepare_once(d);
@@ -126,44 +165,10 @@ int device_prepare(Ctx* ctx, Device* d) {
   return GP_OK;
 }
 
-void free_arena(Device* d) {
-  if (d->arena) {
-    cudaSetDevice(d->ordinal);
-    cudaFree(d->arena);
-  }
-  d->arena = nullptr;
-  d->arena_bytes = 0;
-  d->triad_operands_bytes = 0;
-}
-
 static uint64_t cfg_hbm_bytes(const Ctx* c) { return c->cfg.hbm_bytes ? c->cfg.hbm_bytes : (16ull << 30); }
 static uint64_t cfg_pattern_bytes(const Ctx* c) {
   return c->cfg.pattern_bytes ? c->cfg.pattern_bytes : cfg_hbm_bytes(c);
 }
-static uint64_t cfg_arena_cap(const Ctx* c) {
-  return c->cfg.arena_cap_bytes ? c->cfg.arena_cap_bytes : 5 * cfg_hbm_bytes(c) + (1ull << 30);
-}
-
-int ensure_arena(Ctx* ctx, Device* d, size_t bytes, bool ignore_cap) {
-  if (bytes <= d->arena_bytes) return GP_OK;
-  if (!ignore_cap && bytes > cfg_arena_cap(ctx)) {
-    set_error("arena request %zu exceeds cap %llu", bytes, (unsigned long long)cfg_arena_cap(ctx));
-    return GP_ERR_NOMEM;
-  }
-  free_arena(d);
-  size_t free_b = 0, total_b = 0;
-  CU_OR_RETURN(cudaMemGetInfo(&free_b, &total_b), nullptr);
-  if (bytes > free_b) {
-    set_error("arena request %zu exceeds free device memory %zu", bytes, free_b);
-    return GP_ERR_NOMEM;
-  }
-  void* p = nullptr;
-  CU_OR_RETURN(cudaMalloc(&p, bytes), nullptr);
-  d->arena = reinterpret_cast<uint8_t*>(p);
-  d->arena_bytes = bytes;
-  return GP_OK;
-}
-
 void summarize(const std::vector<float>& ms, gp_timing* t) {
   if (!t) return;
   memset(t, 0, sizeof(*t));
@@ -338,6 +343,9 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
   Locked L(ctx, uuid);
   if (L.rc) { out->error = L.rc; return L.rc; }
   Device* d = L.d;
+  d->alloc_s = 0;
+  d->free_s = 0;
+  out->arena_reused = d->arena != nullptr;
   snprintf(out->uuid, sizeof(out->uuid), "%s", d->uuid);
   out->ordinal = d->ordinal;
   out->sm_count = d->sm_count;
@@ -362,11 +370,20 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
   out->hbm_bytes = hbm;
   out->pattern_bytes = pat;
   int rc = GP_OK;
+  auto finish = [&] {
+    out->arena_bytes = d->arena_bytes;
+    out->arena_backend = d->arena ? (d->arena_is_vmm ? GP_ARENA_VMM : GP_ARENA_MALLOC) : 0;
+    if (!ctx->cfg.keep_arena) free_arena(d);
+    out->duration_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    out->alloc_s = d->alloc_s;
+    out->free_s = d->free_s;
+    out->kernels_s = out->duration_s - out->alloc_s - out->free_s;
+  };
   auto fail = [&](int code) {
     out->error = code;
     out->healthy = 0;
-    if (!ctx->cfg.keep_arena) free_arena(d);
-    out->duration_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (code == GP_ERR_DEVICE_LOST) { d->poisoned = true; d->poison_code = (int)out->detail; }
+    finish();
     return code;
   };
 
@@ -378,7 +395,8 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
     if (mask & GP_PROBE_PATTERN) need = std::max<uint64_t>(need, pat);
     if (mask & GP_PROBE_GEMM) {
       const uint64_t g = ctx->cfg.gemm_mnk ? ctx->cfg.gemm_mnk : 8192;
-      need = std::max<uint64_t>(need, 8 * g * g + (4ull << 20));  // A + B (2 B) + C (4 B) + check vectors
+      // A + B (2 B each) + C fp32 (4 B) [+ C bf16 (2 B)] + check vectors
+      need = std::max<uint64_t>(need, (ctx->cfg.gemm_output == 1 ? 10 : 8) * g * g + (4ull << 20));
     }
     if (need > d->arena_bytes && (need <= cfg_arena_cap(ctx) || pat_all)) {
       rc = ensure_arena(ctx, d, need, /*ignore_cap=*/pat_all);
@@ -456,8 +474,7 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
       out->failed_mask |= GP_PROBE_GEMM;
   }
   out->healthy = out->failed_mask == 0;
-  if (!ctx->cfg.keep_arena) free_arena(d);
-  out->duration_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  finish();
   return GP_OK;
 }
 
@@ -479,6 +496,7 @@ size_t gp_sizeof(int which) {
     case 4: return sizeof(gp_device_result);
     case 5: return sizeof(gp_kernel_stat);
     case 6: return sizeof(gp_nvml_info);
+    case 7: return sizeof(gp_fabric_result);
     default: return 0;
   }
 }
@@ -494,6 +512,7 @@ const char* gp_strerror(int err) {
     case GP_ERR_UNSUPPORTED: return "unsupported on this device";
     case GP_ERR_STRUCT_SIZE: return "struct size / ABI version mismatch";
     case GP_ERR_TOO_LARGE: return "request exceeds a fixed limit";
+    case GP_ERR_DEVICE_LOST: return "device lost to a sticky CUDA fault";
     default: return "unknown error";
   }
 }
@@ -529,6 +548,7 @@ int gp_init(const gp_config* cfg, gp_ctx** out) {
     d->ordinal = i;
     format_uuid(p.uuid, d->uuid, sizeof(d->uuid));
     d->sm_count = p.multiProcessorCount;
+    if (c.sm_limit && (int)c.sm_limit < d->sm_count) d->sm_count = (int)c.sm_limit;
     d->cc_major = p.major;
     d->cc_minor = p.minor;
     d->total_mem = p.totalGlobalMem;
@@ -543,10 +563,9 @@ void gp_shutdown(gp_ctx* ctx) {
   nccl_teardown(ctx);
   for (auto& d : ctx->devs) {
     std::lock_guard<std::mutex> g(d->mu);
-    if (!d->ready && !d->arena) continue;
+    if (!d->ready && !d->arena && !d->va_base) continue;
     cudaSetDevice(d->ordinal);
-    if (d->stream) cudaStreamSynchronize(d->stream);
-    free_arena(d.get());
+    if (d->stream && !d->poisoned) cudaStreamSynchronize(d->stream);
     device_release(d.get());
   }
   delete ctx;
@@ -560,6 +579,59 @@ int gp_trim(gp_ctx* ctx) {
     free_arena(d.get());
   }
   return GP_OK;
+}
+
+int gp_trim_device(gp_ctx* ctx, const char* uuid) {
+  Device* d = find_device(ctx, uuid);
+  if (!d) { set_error("device '%s' is not visible to CUDA", uuid ? uuid : "(null)"); return ctx ? GP_ERR_NO_DEVICE : GP_ERR_INVALID; }
+  std::lock_guard<std::mutex> g(d->mu);
+  if (d->stream && !d->poisoned) { cudaSetDevice(d->ordinal); cudaStreamSynchronize(d->stream); }
+  free_arena(d);
+  return GP_OK;
+}
+
+int gp_device_poisoned(gp_ctx* ctx, const char* uuid) {
+  Device* d = find_device(ctx, uuid);
+  if (!d) return ctx ? GP_ERR_NO_DEVICE : GP_ERR_INVALID;
+  std::lock_guard<std::mutex> g(d->mu);
+  return (d->poisoned || (poisoned_ordinals() >> d->ordinal & 1)) ? 1 : 0;
+}
+
+int gp_device_reset(gp_ctx* ctx, const char* uuid) {
+  Device* d = find_device(ctx, uuid);
+  if (!d) { set_error("device '%s' is not visible to CUDA", uuid ? uuid : "(null)"); return ctx ? GP_ERR_NO_DEVICE : GP_ERR_INVALID; }
+  std::lock_guard<std::mutex> multi(ctx->multi_mu);
+  std::lock_guard<std::mutex> g(d->mu);
+  cudaError_t e = cudaSetDevice(d->ordinal);
+  (void)e;
+  // every handle below belongs to the context that is about to die; failures while dropping them are expected
+  device_release(d);
+  (void)cudaGetLastError();
+  nccl_teardown(ctx);  // communicators hold streams and buffers in the old context
+  noalloc_forget_device(d->ordinal);
+  e = cudaDeviceReset();
+  if (e != cudaSuccess) {
+    set_error("cudaDeviceReset: %s (%d)", cudaGetErrorString(e), (int)e);
+    (void)cudaGetLastError();
+    return GP_ERR_DEVICE_LOST;
+  }
+  d->poisoned = false;
+  d->poison_code = 0;
+  clear_poisoned_ordinal(d->ordinal);
+  memset(d->stats, 0, sizeof(d->stats));
+  return GP_OK;
+}
+
+int gp_inject_cuda_error(gp_ctx* ctx, const char* uuid, int cuda_error) {
+  Device* d = find_device(ctx, uuid);
+  if (!d) return ctx ? GP_ERR_NO_DEVICE : GP_ERR_INVALID;
+  std::lock_guard<std::mutex> g(d->mu);
+  cudaError_t e = cudaSetDevice(d->ordinal);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice", nullptr);
+  int64_t detail = 0;
+  const int rc = cuda_fail((cudaError_t)cuda_error, "injected fault (gp_inject_cuda_error)", &detail);
+  if (rc == GP_ERR_DEVICE_LOST) { d->poisoned = true; d->poison_code = cuda_error; }
+  return rc;
 }
 
 int gp_device_count(gp_ctx* ctx) { return ctx ? (int)ctx->devs.size() : GP_ERR_INVALID; }
@@ -820,8 +892,13 @@ int gp_inject_bitflip(gp_ctx* ctx, const char* uuid, uint64_t word_index, int bi
 }
 
 int gp_probe_p2p(gp_ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps_out) {
-  if (!ctx || !gbps_out || ngpus < 1 || dir < 0 || dir > 4) { set_error("bad arguments"); return GP_ERR_INVALID; }
+  if (!ctx || !gbps_out || ngpus < 1 || dir < 0 || dir > 6) { set_error("bad arguments"); return GP_ERR_INVALID; }
   return p2p_probe(ctx, ngpus, bytes, dir, gbps_out);
+}
+
+int gp_probe_fabric(gp_ctx* ctx, int ngpus, gp_fabric_result* out) {
+  if (!ctx || !out || ngpus < 1 || ngpus > GP_FABRIC_MAX_GPUS) { set_error("bad arguments (1 <= ngpus <= %d)", GP_FABRIC_MAX_GPUS); return GP_ERR_INVALID; }
+  return fabric_probe(ctx, ngpus, out);
 }
 
 int gp_probe_allreduce(gp_ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters,

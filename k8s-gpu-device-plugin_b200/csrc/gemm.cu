@@ -14,9 +14,16 @@
 //     kStages shared-memory stages, completion counted on mbarriers;
 //   * warp 1: allocates the 512 TMEM columns, and its elected lane issues tcgen05.mma
 //     (kind::f16, bf16 x bf16 -> fp32), releasing stages with tcgen05.commit;
-//   * warps 2-5: epilogue, tcgen05.ld 32 lanes x 32 columns at a time -> registers ->
-//     256-bit st.global (one full L2 sector per lane); two accumulator stages (2 x 256 TMEM columns) so the epilogue of tile t
-//     overlaps the main loop of tile t+1.
+//   * warps 2-9: epilogue, two sets of four warps (a warp may only read TMEM lanes 32 (w % 4) ..+32); each
+//     set drains 128 of the 256 columns of an accumulator half: tcgen05.ld 32 lanes x 32 columns at a time
+//     (the next load in flight while the previous chunk is stored) -> registers -> 256-bit st.global, one
+//     full L2 sector per lane per store, four stores completing a 128-byte line;
+//   * each 256-column half of the TMEM accumulator has its own full/empty barrier pair: with 256 x 256
+//     tiles the halves are two accumulator stages (tile t+1 accumulates while tile t drains); with the
+//     256 x 512 tile both halves belong to one tile, the epilogue releases half 0 first, and the MMA
+//     thread starts the next tile's nt = 0 MMAs as soon as half 0 is free, running up to kStages - 1
+//     k-blocks ahead of the nt = 1 MMAs, which catch up once half 1 is drained (round 1 waited for all
+//     512 columns: tensor pipe 91.8 % active against 96.7 % for the double-buffered 256 x 256 kernel).
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -37,7 +44,8 @@ constexpr int kBlockM = 128;  // rows of A (and of the accumulator) per CTA
 constexpr int kBlockK = 64;   // 64 bf16 = 128 bytes = one swizzle span
 constexpr int kUmmaK = 16;    // K per tcgen05.mma for 16-bit inputs
 constexpr int kTileN = 256;   // accumulator columns per tile (UMMA N)
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 8;   // two sets of four (one warp per TMEM lane quarter per set)
+constexpr int kGemmThreads = 32 * (2 + kEpiWarps);
 
 // CG = CTAs per MMA (tcgen05 cta_group), NT = 256-wide N sub-tiles accumulated per tile.
 // NT = 2 keeps BOTH 256-column TMEM accumulators busy with one 256 x 512 tile that shares every
@@ -51,13 +59,13 @@ struct GemmCfg {
   static constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
   static constexpr uint32_t kBBytes = kLoadN * kBlockK * 2;
   static constexpr uint32_t kStageBytes = kABytes + NT * kBBytes;
-  static constexpr int kStages = (192 * 1024) / kStageBytes;  // 6 x 32 KiB, 4 x 48 KiB
+  static constexpr int kStages = (224 * 1024) / kStageBytes;  // 7 x 32 KiB, 4 x 48 KiB (the epilogue needs no staging)
   static constexpr uint32_t kTxBytes = kStageBytes * CG;  // bytes landing per stage on the leader's barrier
-  static constexpr uint32_t kEpiBytes = 2 * 4 * 4096;  // 2 buffers x 4 epilogue warps x (32 rows x 128 B)
-  static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr size_t kSmemBytes = (size_t)kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
   static constexpr int kTileM = kBlockM * CG;
   static constexpr int kTileNAll = kTileN * NT;   // output columns per tile
-  static constexpr int kAccStages = 2 / NT;       // TMEM: 512 columns = kAccStages x kTileNAll
+  static constexpr int kAccStages = 2 / NT;       // TMEM: 512 columns = kAccStages x kTileNAll = 2 halves of 256
+  static constexpr int kLead = kStages - 1;       // k-blocks the nt = 0 MMAs may run ahead of nt = 1 (NT == 2)
 };
 
 // ------------------------------------------------------------ PTX helpers ---
@@ -116,6 +124,21 @@ __device__ __forceinline__ void st_f8_hint(float* p, const float* v, uint64_t po
   asm volatile("st.global.L1::no_allocate.L2::cache_hint.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;" ::"l"(p),
                "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]), "l"(pol)
                : "memory");
+}
+__device__ __forceinline__ void st_u8_hint(void* p, const uint32_t* v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;" ::"l"(p),
+               "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "l"(pol)
+               : "memory");
+}
+// non-blocking: has the phase with this parity completed?
+__device__ __forceinline__ bool mbar_test_addr(uint32_t bar_smem_addr, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar_smem_addr), "r"(parity) : "memory");
+  return ok != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -209,19 +232,16 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
 template <int CG, int NT, int OUT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 const __grid_constant__ CUtensorMap map_c, float* __restrict__ C, int M, int N, int K,
-                 int group_m, int hints) {
+                 void* __restrict__ Cv, int M, int N, int K, int group_m, int hints) {
   using Cfg = GemmCfg<CG, NT>;
-  constexpr int kAccStages = Cfg::kAccStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle-128B needs 1024-byte alignment
-  const uint32_t epi_base = smem_base + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned: stage bytes are multiples of 1024
-  const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
+  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
-  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * Cfg::kStages + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * Cfg::kStages + kAccStages + a); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * Cfg::kStages + 2 * kAccStages);
+  auto tfull_bar = [&](int h) { return bar_base + 8u * (2 * Cfg::kStages + h); };       // per 256-column half
+  auto tempty_bar = [&](int h) { return bar_base + 8u * (2 * Cfg::kStages + 2 + h); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * Cfg::kStages + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0;
@@ -230,14 +250,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
-    tma_prefetch_desc(&map_c);
     for (int s = 0; s < Cfg::kStages; ++s) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(full_bar(s)));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty_bar(s)));
     }
-    for (int a = 0; a < kAccStages; ++a) {
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tfull_bar(a)));
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tempty_bar(a)), "r"(4 * CG));
+    for (int h = 0; h < 2; ++h) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tfull_bar(h)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tempty_bar(h)), "r"(kEpiWarps * CG));
     }
     mbar_fence_init();
   }
@@ -252,14 +271,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const int num_tiles = tiles_m * tiles_n;
   const int num_kb = K / kBlockK;
   const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
-  // raster: groups of kGroupM tile rows, columns fastest inside a group, so that the ~148 tiles
-  // in flight share A and B panels that fit in L2 together
+  // raster: groups of group_m tile rows, rows fastest inside a group, so that the tiles in flight share
+  // A and B panels that fit in L2 together; odd groups walk the columns backwards (serpentine) so the B
+  // panels at a group boundary are still in L2 when the next group starts
   auto tile_coords = [&](int t, int& tm, int& tn) {
     const int per_group = group_m * tiles_n;
     const int g = t / per_group, r = t % per_group;
     const int rows = min(group_m, tiles_m - g * group_m);
     tm = g * group_m + r % rows;
     tn = r / rows;
+    if (g & 1) tn = tiles_n - 1 - tn;
   };
 
   if (warp == 0) {
@@ -293,137 +314,140 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // ============================= MMA issuer =============================
     if (leader && elect_one()) {
       constexpr uint32_t idesc = make_idesc(Cfg::kTileM, kTileN);
-      int stage = 0; uint32_t phase = 0;
-      int acc = 0; uint32_t acc_phase = 0;
-      for (int t = unit; t < num_tiles; t += num_units) {
-        mbar_wait_addr(tempty_bar(acc), acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::kTileNAll);
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait_addr(full_bar(stage), phase);
+      // the four MMAs (K = 64 in steps of 16) of one N sub-tile over one stage
+      auto mma_sub = [&](int stage, int nt, uint32_t d_tmem, bool first_kb) {
+        const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
+        const uint64_t adesc = make_smem_desc(sa);
+        const uint64_t bdesc = make_smem_desc(sa + Cfg::kABytes + nt * Cfg::kBBytes);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k)  // +32 bytes per K step of 16 bf16 -> +2 in the 16-byte-unit address field
+          umma_f16<CG>(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (uint32_t)(!first_kb || k != 0));
+      };
+      if constexpr (NT == 1) {
+        int stage = 0; uint32_t phase = 0;
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int t = unit; t < num_tiles; t += num_units) {
+          mbar_wait_addr(tempty_bar(acc), acc_phase ^ 1);
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
-          const uint64_t adesc = make_smem_desc(sa);
-#pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-              // +32 bytes per K step of 16 bf16 -> +2 in the 16-byte-unit address field
-              const uint64_t bdesc = make_smem_desc(sa + Cfg::kABytes + nt * Cfg::kBBytes);
-              umma_f16<CG>(d_tmem + (uint32_t)(nt * kTileN), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k),
-                           idesc, (uint32_t)((kb | k) != 0));
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kTileN);
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait_addr(full_bar(stage), phase);
+            tc_fence_after();
+            mma_sub(stage, 0, d_tmem, kb == 0);
+            umma_commit<CG>(empty_bar(stage));  // frees the stage once these MMAs have read it
+            if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+          }
+          umma_commit<CG>(tfull_bar(acc));      // accumulator complete -> epilogue
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+      } else {
+        // 256 x 512 tile: half h of TMEM holds N sub-tile h.  s0 / s1 are the stage cursors of the nt = 0 and
+        // nt = 1 MMAs; nt = 0 may lead by up to kLead stages while the epilogue is still draining half 1.
+        int s0 = 0, s1 = 0; uint32_t ph0 = 0;
+        uint32_t acc_phase = 0;
+        for (int t = unit; t < num_tiles; t += num_units) {
+          mbar_wait_addr(tempty_bar(0), acc_phase ^ 1);
+          tc_fence_after();
+          bool half1_free = false;
+          int kb0 = 0, kb1 = 0;
+          while (kb1 < num_kb) {
+            if (!half1_free) {
+              half1_free = mbar_test_addr(tempty_bar(1), acc_phase ^ 1);
+              if (!half1_free && (kb0 - kb1 >= Cfg::kLead || kb0 == num_kb)) {
+                mbar_wait_addr(tempty_bar(1), acc_phase ^ 1);
+                half1_free = true;
+              }
+              if (half1_free) tc_fence_after();
+            }
+            if (!half1_free) {  // run ahead with nt = 0 only
+              mbar_wait_addr(full_bar(s0), ph0);
+              tc_fence_after();
+              mma_sub(s0, 0, tmem_base, kb0 == 0);
+              if (kb0 == num_kb - 1) umma_commit<CG>(tfull_bar(0));
+              if (++s0 == Cfg::kStages) { s0 = 0; ph0 ^= 1; }
+              ++kb0;
+            } else if (kb1 < kb0) {  // catch up: nt = 1 on a stage nt = 0 has already consumed
+              mma_sub(s1, 1, tmem_base + (uint32_t)kTileN, kb1 == 0);
+              umma_commit<CG>(empty_bar(s1));
+              if (kb1 == num_kb - 1) umma_commit<CG>(tfull_bar(1));
+              if (++s1 == Cfg::kStages) s1 = 0;
+              ++kb1;
+            } else {  // in step: both sub-tiles over the same stage (A is read from shared memory for both)
+              mbar_wait_addr(full_bar(s0), ph0);
+              tc_fence_after();
+              mma_sub(s0, 0, tmem_base, kb0 == 0);
+              if (kb0 == num_kb - 1) umma_commit<CG>(tfull_bar(0));  // half 0 can drain while half 1 finishes
+              mma_sub(s0, 1, tmem_base + (uint32_t)kTileN, kb0 == 0);
+              umma_commit<CG>(empty_bar(s0));
+              if (kb0 == num_kb - 1) umma_commit<CG>(tfull_bar(1));
+              if (++s0 == Cfg::kStages) { s0 = 0; ph0 ^= 1; }
+              s1 = s0;
+              ++kb0; ++kb1;
             }
           }
-          umma_commit<CG>(empty_bar(stage));  // frees the stage once these MMAs have read it
-          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+          acc_phase ^= 1;
         }
-        umma_commit<CG>(tfull_bar(acc));      // accumulator complete -> epilogue
-        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else {
     // ============================== epilogue ==============================
-    const int quarter = warp & 3;  // a warp may only touch TMEM lanes [32 q, 32 q + 32)
-    int acc = 0; uint32_t acc_phase = 0;
+    const int quarter = warp & 3;       // a warp may only touch TMEM lanes [32 q, 32 q + 32)
+    const int set = (warp - 2) >> 2;    // which 128 columns of every 256-column half this warp drains
     const uint32_t tempty_leader = CG == 2 ? map_to_cta(tempty_bar(0), 0) : tempty_bar(0);
     const uint64_t pol_c = l2_policy((hints >> 4) & 3);
-    uint32_t epi_count = 0;
+    int acc = 0; uint32_t acc_phase = 0;  // NT == 1: accumulator stage of this tile; NT == 2: phase only
     for (int t = unit; t < num_tiles; t += num_units) {
       int tm, tn;
       tile_coords(t, tm, tn);
-      mbar_wait_addr(tfull_bar(acc), acc_phase);
-      tc_fence_after();
       const int row = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32 + lane;
-      float* crow = C + (size_t)row * N + (size_t)tn * Cfg::kTileNAll;
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * Cfg::kTileNAll);
-      if constexpr (OUT == 1) {
-        // bf16 output: 64 accumulator columns -> one 128-byte staging row per lane -> TMA store of a
-        // 32 x 64 bf16 box; same swizzle and double buffering as the fp32 path below
-        const int ewarp = warp - 2;
-        const int tile_row0 = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32;
 #pragma unroll 1
-        for (int c = 0; c < Cfg::kTileNAll / 64; ++c) {
-          float v0[32], v1[32];
-          tmem_ld_32x32(taddr + (uint32_t)(c * 64), v0);
-          tmem_ld_32x32(taddr + (uint32_t)(c * 64 + 32), v1);
-          const uint32_t buf = epi_base + (uint32_t)(((epi_count & 1) * 4 + ewarp) * 4096);
-          if (lane == 0) bulk_wait_read<1>();
-          __syncwarp();
-          tmem_ld_wait();
-          uint32_t w[32];
+      for (int h = 0; h < NT; ++h) {
+        const int b = NT == 2 ? h : acc;  // TMEM half == barrier index
+        mbar_wait_addr(tfull_bar(b), acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(b * kTileN + set * 128);
+        const size_t col0 = (size_t)tn * Cfg::kTileNAll + (size_t)(h * kTileN + set * 128);
+        if constexpr (OUT == 0) {
+          float* crow = reinterpret_cast<float*>(Cv) + (size_t)row * N + col0;
+          float v[2][32];
+          tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[i]) : "f"(v0[2 * i + 1]), "f"(v0[2 * i]));
-            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[16 + i]) : "f"(v1[2 * i + 1]), "f"(v1[2 * i]));
-          }
+          for (int c = 0; c < 4; ++c) {
+            tmem_ld_wait();
+            if (c + 1 < 4) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t addr = buf + (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4));
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(w[4 * j]), "r"(w[4 * j + 1]),
-                         "r"(w[4 * j + 2]), "r"(w[4 * j + 3]) : "memory");
+            for (int q = 0; q < 4; ++q) st_f8_hint(crow + c * 32 + q * 8, v[c & 1] + 8 * q, pol_c);
           }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            asm volatile(
-                "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(&map_c),
-                "r"(buf), "r"(tn * Cfg::kTileNAll + c * 64), "r"(tile_row0), "l"(pol_c)
-                : "memory");
-            bulk_commit();
+        } else {
+          uint16_t* crow = reinterpret_cast<uint16_t*>(Cv) + (size_t)row * N + col0;
+          float v[2][64];
+          tmem_ld_32x32(taddr, v[0]);
+          tmem_ld_32x32(taddr + 32u, v[0] + 32);
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            tmem_ld_wait();
+            if (c + 1 < 2) {
+              tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 64), v[(c + 1) & 1]);
+              tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 64 + 32), v[(c + 1) & 1] + 32);
+            }
+            uint32_t w[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[i]) : "f"(v[c & 1][2 * i + 1]), "f"(v[c & 1][2 * i]));
+#pragma unroll
+            for (int q = 0; q < 4; ++q) st_u8_hint(crow + c * 64 + q * 16, w + 8 * q, pol_c);
           }
-          ++epi_count;
         }
-      } else if (hints & 128) {  // development path: direct 256-bit stores from registers
-#pragma unroll 1
-        for (int c = 0; c < Cfg::kTileNAll / 32; ++c) {
-          float v[32];
-          tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
-          tmem_ld_wait();
-          if (!(hints & 64) || v[0] == 123.456f)
-#pragma unroll
-            for (int q = 0; q < 4; ++q) st_f8_hint(crow + c * 32 + q * 8, v + 8 * q, pol_c);
-        }
-      } else {
-        // registers -> this warp's 32 x 32 fp32 staging tile (128-byte rows, 16-byte chunks XOR-swizzled
-        // by row & 7 exactly as the tensor map's SWIZZLE_128B expects, which also makes the st.shared.v4
-        // conflict-free) -> one TMA store per chunk; two staging buffers per warp
-        const int ewarp = warp - 2;
-        const int tile_row0 = tm * Cfg::kTileM + (int)cta_rank * kBlockM + quarter * 32;
-#pragma unroll 1
-        for (int c = 0; c < Cfg::kTileNAll / 32; ++c) {
-          float v[32];
-          tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
-          const uint32_t buf = epi_base + (uint32_t)(((epi_count & 1) * 4 + ewarp) * 4096);
-          if (lane == 0) bulk_wait_read<1>();  // the store that last used this buffer has read it
-          __syncwarp();
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t addr = buf + (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4));
-            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v[4 * j]), "f"(v[4 * j + 1]),
-                         "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
-          }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            asm volatile(
-                "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(&map_c),
-                "r"(buf), "r"(tn * Cfg::kTileNAll + c * 32), "r"(tile_row0), "l"(pol_c)
-                : "memory");
-            bulk_commit();
-          }
-          ++epi_count;
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CG == 2) mbar_arrive_cluster(tempty_leader + 8u * b);
+          else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty_bar(b)) : "memory");
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if constexpr (CG == 2) mbar_arrive_cluster(tempty_leader + 8u * acc);
-        else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty_bar(acc)) : "memory");
-      }
-      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+      if constexpr (NT == 2) { acc_phase ^= 1; }
+      else { if (++acc == 2) { acc = 0; acc_phase ^= 1; } }
     }
-    if (lane == 0) bulk_wait_all<0>();  // this warp's TMA stores have completed
   }
 
   tc_fence_before();
@@ -525,18 +549,12 @@ static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
   return GP_OK;
 }
 
-static int gemm_cta_group() {
-  const char* e = getenv("GPUPROBE_GEMM_CTA_GROUP");  // development switch; default is the 2-CTA kernel
-  if (e && e[0] == '1') return 1;
-  return 2;
-}
-
 template <int CG, int NT, int OUT>
-static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, float* C,
-                                  int M, int N, int K, int sm_count, cudaStream_t stream) {
+static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, void* C, int M, int N, int K,
+                                  int sm_count, cudaStream_t stream) {
   using Cfg = GemmCfg<CG, NT>;
   const int tiles = (M / Cfg::kTileM) * (N / Cfg::kTileNAll);
-  int units = std::min(tiles, sm_count / CG);
+  int units = std::max(1, std::min(tiles, sm_count / CG));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(units * CG));
   cfg.blockDim = dim3(kGemmThreads);
@@ -549,16 +567,16 @@ static cudaError_t launch_gemm_cg(const CUtensorMap& ma, const CUtensorMap& mb, 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  // raster group height in tile rows (development override: GPUPROBE_GEMM_GROUP_M)
-  static const int env_group = getenv("GPUPROBE_GEMM_GROUP_M") ? atoi(getenv("GPUPROBE_GEMM_GROUP_M")) : 0;
-  // measured at 8192^3: 256x256 tiles 4: 1430, 8: 1475, 16: 1458; 256x512 tiles 4: 1493, 8: 1529, 16: 1540, 32: 1519
+  // raster group height in tile rows.  Measured at 8192^3 (round 1): 256x256 tiles 4: 1430, 8: 1475, 16: 1458;
+  // 256x512 tiles 4: 1493, 8: 1529, 16: 1540, 32: 1519 TFLOP/s
+  static const int env_group = GP_DEV_SWITCH("GPUPROBE_GEMM_GROUP_M", 0);
   const int group_m = env_group > 0 ? env_group : (NT == 2 ? 16 : 16 / CG);
-  // L2 policies, 2 bits each for A | B << 2 | C << 4 (0 normal, 1 evict_last, 2 evict_first)
-  static const int env_hints = getenv("GPUPROBE_GEMM_HINTS") ? atoi(getenv("GPUPROBE_GEMM_HINTS")) : -1;
-  // measured at 8192^3, 20 launches each: operands evict_last + C evict_first 1462 TFLOP/s median,
-  // no hints 1438; operand panels are re-read by the next wave, C is written once and never read
+  // L2 policies, 2 bits each for A | B << 2 | C << 4 (0 normal, 1 evict_last, 2 evict_first).  Measured at
+  // 8192^3, 20 launches each: operands evict_last + C evict_first 1462 TFLOP/s median, no hints 1438; operand
+  // panels are re-read by the next wave, C is written once and never read
+  static const int env_hints = GP_DEV_SWITCH("GPUPROBE_GEMM_HINTS", -1);
   const int hints = env_hints >= 0 ? env_hints : (1 | (1 << 2) | (2 << 4));
-  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG, NT, OUT>, ma, mb, mc, C, M, N, K, group_m, hints);
+  return cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<CG, NT, OUT>, ma, mb, C, M, N, K, group_m, hints);
 }
 
 // function attributes are per device: called once from device_prepare with the device current
@@ -579,53 +597,37 @@ cudaError_t gemm_kernels_configure() {
 
 struct GemmPlan {
   int cg, nt, out;
-  CUtensorMap ma, mb, mc;
+  CUtensorMap ma, mb;
 };
 
-// C (row-major M x N) as a 2-D map with 128-byte box rows (32 fp32 or 64 bf16) x 32 rows, 128-byte swizzle
-static int make_map_c(CUtensorMap* map, const void* base, uint64_t M, uint64_t N, bool out_bf16) {
-  EncodeTiledFn enc = get_encode_fn();
-  if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return GP_ERR_UNSUPPORTED; }
-  const cuuint64_t dims[2] = {N, M};
-  const cuuint64_t strides[1] = {N * (out_bf16 ? 2u : 4u)};
-  const cuuint32_t box[2] = {out_bf16 ? 64u : 32u, 32};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = enc(map, out_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
-                         const_cast<void*>(base), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (C) failed: %d", (int)r); return GP_ERR_CUDA; }
-  return GP_OK;
-}
-
-static int make_plan(GemmPlan* p, const void* A, const void* B, const void* C, uint32_t m, uint32_t n, uint32_t k,
-                     bool out_bf16) {
+// variant: GP_GEMM_* of gp_config.gemm_variant
+static int make_plan(GemmPlan* p, const void* A, const void* B, uint32_t m, uint32_t n, uint32_t k, bool out_bf16,
+                     uint32_t variant) {
   p->out = out_bf16 ? 1 : 0;
-  p->cg = gemm_cta_group();
-  // 256 x 512 tiles (two N sub-tiles per CTA pair) whenever the shape allows; GPUPROBE_GEMM_NT=1 forces 256 x 256
-  static const int env_nt = getenv("GPUPROBE_GEMM_NT") ? atoi(getenv("GPUPROBE_GEMM_NT")) : 0;
-  p->nt = (p->cg == 2 && n % 512 == 0 && env_nt != 1) ? 2 : 1;
+  p->cg = variant == GP_GEMM_1CTA_128x256 ? 1 : 2;
+  // 256 x 512 tiles (two N sub-tiles per CTA pair) whenever the shape allows
+  p->nt = (p->cg == 2 && n % 512 == 0 && variant != GP_GEMM_2CTA_256x256) ? 2 : 1;
+  if (variant > GP_GEMM_2CTA_256x512) { set_error("unknown gemm_variant %u", variant); return GP_ERR_INVALID; }
   if (m % 256 || n % 256 || k % 64 || m == 0 || n == 0 || k == 0) {
     set_error("gemm needs m, n multiples of 256 and k a multiple of 64");
     return GP_ERR_INVALID;
   }
   int rc = make_map(&p->ma, A, m, k, kBlockM);
   if (rc) return rc;
-  rc = make_map_c(&p->mc, C, m, n, out_bf16);
-  if (rc) return rc;
   return make_map(&p->mb, B, n, k, (uint32_t)(kTileN / p->cg));
 }
 
-static cudaError_t launch_gemm(const GemmPlan& p, float* C, int M, int N, int K, int sm_count,
+// out_bf16 overrides the plan's output type: the bf16 probe also runs the fp32 kernel of the same plan once
+static cudaError_t launch_gemm(const GemmPlan& p, bool out_bf16, void* C, int M, int N, int K, int sm_count,
                                cudaStream_t stream) {
-  if (p.out) {
-    if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
-    return p.cg == 2 ? launch_gemm_cg<2, 1, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
-                     : launch_gemm_cg<1, 1, 1>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+  if (out_bf16) {
+    if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2, 1>(p.ma, p.mb, C, M, N, K, sm_count, stream);
+    return p.cg == 2 ? launch_gemm_cg<2, 1, 1>(p.ma, p.mb, C, M, N, K, sm_count, stream)
+                     : launch_gemm_cg<1, 1, 1>(p.ma, p.mb, C, M, N, K, sm_count, stream);
   }
-  if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2, 0>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
-  return p.cg == 2 ? launch_gemm_cg<2, 1, 0>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream)
-                   : launch_gemm_cg<1, 1, 0>(p.ma, p.mb, p.mc, C, M, N, K, sm_count, stream);
+  if (p.cg == 2 && p.nt == 2) return launch_gemm_cg<2, 2, 0>(p.ma, p.mb, C, M, N, K, sm_count, stream);
+  return p.cg == 2 ? launch_gemm_cg<2, 1, 0>(p.ma, p.mb, C, M, N, K, sm_count, stream)
+                   : launch_gemm_cg<1, 1, 0>(p.ma, p.mb, C, M, N, K, sm_count, stream);
 }
 
 #define CU_OR_RETURN(call)                                               \
@@ -648,23 +650,48 @@ int gemm_host_locked(Ctx* ctx, Device* d, const uint16_t* a, const uint16_t* b, 
   if (rc) return rc;
   const size_t a_bytes = (size_t)m * k * 2, b_bytes = (size_t)n * k * 2, c_bytes = (size_t)m * n * 4;
   auto up = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
+  GemmPlan plan;
   rc = ensure_arena(ctx, d, up(a_bytes) + up(b_bytes) + up(c_bytes));
   if (rc) return rc;
   d->triad_operands_bytes = 0;
   uint8_t* A = d->arena;
   uint8_t* B = A + up(a_bytes);
   float* C = reinterpret_cast<float*>(B + up(b_bytes));
-  GemmPlan plan;
-  rc = make_plan(&plan, A, B, C, m, n, k, /*out_bf16=*/false);
+  rc = make_plan(&plan, A, B, m, n, k, /*out_bf16=*/false, ctx->cfg.gemm_variant);
   if (rc) return rc;
   CU_OR_RETURN(cudaMemcpyAsync(A, a, a_bytes, cudaMemcpyHostToDevice, d->stream));
   CU_OR_RETURN(cudaMemcpyAsync(B, b, b_bytes, cudaMemcpyHostToDevice, d->stream));
   CU_OR_RETURN(cudaMemsetAsync(C, 0xFF, c_bytes, d->stream));
-  CU_OR_RETURN(launch_gemm(plan, C, (int)m, (int)n, (int)k, d->sm_count, d->stream));
+  CU_OR_RETURN(launch_gemm(plan, false, C, (int)m, (int)n, (int)k, d->sm_count, d->stream));
   CU_OR_RETURN(cudaMemcpyAsync(c, C, c_bytes, cudaMemcpyDeviceToHost, d->stream));
   CU_OR_RETURN(cudaStreamSynchronize(d->stream));
   d->stats[GP_K_GEMM].launches += 1;
   return GP_OK;
+}
+
+// bf16 C against the fp32 C of the same plan: the accumulators are the same bits (same tiles, same K
+// order), so C16 must equal RNE(C32) element for element.  Counts the elements that do not.
+__global__ void bf16_vs_f32_kernel(const uint32_t* __restrict__ c16 /*pairs*/, const float2* __restrict__ c32,
+                                   uint64_t npairs, unsigned long long* __restrict__ bad) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  unsigned long long b = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npairs; i += stride) {
+    const float2 f = c32[i];
+    uint32_t w;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(f.y), "f"(f.x));
+    const uint32_t g = c16[i];
+    b += ((g & 0xFFFFu) != (w & 0xFFFFu)) + ((g >> 16) != (w >> 16));
+  }
+  b = warp_sum_u64(b);
+  if ((threadIdx.x & 31) == 0 && b) atomicAdd(bad, b);
+}
+// test hook (gp_config.test_fault): put the 0xFF fill back into one 256 x 256 tile, as if its stores had been skipped
+template <class T>
+__global__ void unwrite_tile_kernel(T* __restrict__ C, int N, int row0, int col0) {
+  const int r = blockIdx.x, c = threadIdx.x;
+  T v;
+  memset(&v, 0xFF, sizeof(T));
+  C[(size_t)(row0 + r) * N + col0 + c] = v;
 }
 
 int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t warmup, uint32_t iters,
@@ -679,17 +706,19 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   if (samples > 65536) samples = 65536;
   const bool out_bf16 = ctx->cfg.gemm_output == 1;
   out->output_bf16 = out_bf16 ? 1 : 0;
-  const size_t a_bytes = (size_t)m * k * 2, b_bytes = (size_t)n * k * 2, c_bytes = (size_t)m * n * (out_bf16 ? 2 : 4);
+  const size_t a_bytes = (size_t)m * k * 2, b_bytes = (size_t)n * k * 2;
+  const size_t c32_bytes = (size_t)m * n * 4, c16_bytes = out_bf16 ? (size_t)m * n * 2 : 0;
   auto up = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
   const size_t vec_bytes = up((size_t)std::max(std::max(m, n), k) * sizeof(double));
   const size_t aux = 7 * vec_bytes + up((size_t)samples * 8) + up((size_t)samples * 4);
-  rc = ensure_arena(ctx, d, up(a_bytes) + up(b_bytes) + up(c_bytes) + aux);
+  rc = ensure_arena(ctx, d, up(a_bytes) + up(b_bytes) + up(c32_bytes) + up(c16_bytes) + aux);
   if (rc) return rc;
   d->triad_operands_bytes = 0;
   uint8_t* p = d->arena;
   uint16_t* A = reinterpret_cast<uint16_t*>(p); p += up(a_bytes);
   uint16_t* B = reinterpret_cast<uint16_t*>(p); p += up(b_bytes);
-  float* C = reinterpret_cast<float*>(p); p += up(c_bytes);
+  float* C32 = reinterpret_cast<float*>(p); p += up(c32_bytes);
+  uint16_t* C16 = reinterpret_cast<uint16_t*>(p); p += up(c16_bytes);
   double* u = reinterpret_cast<double*>(p); p += vec_bytes;
   double* ub = reinterpret_cast<double*>(p); p += vec_bytes;
   double* v = reinterpret_cast<double*>(p); p += vec_bytes;
@@ -699,23 +728,42 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   float* xs = reinterpret_cast<float*>(p); p += vec_bytes;
   uint32_t* d_ij = reinterpret_cast<uint32_t*>(p); p += up((size_t)samples * 8);
   float* d_sampled = reinterpret_cast<float*>(p);
+  void* Ctimed = out_bf16 ? (void*)C16 : (void*)C32;
 
   GemmPlan plan;
-  rc = make_plan(&plan, A, B, C, m, n, k, out_bf16);
+  rc = make_plan(&plan, A, B, m, n, k, out_bf16, ctx->cfg.gemm_variant);
   if (rc) return rc;
   cudaStream_t s = d->stream;
   CU_OR_RETURN(launch_gen_bf16(A, (uint64_t)m * k, seed, d->sm_count, s));
   CU_OR_RETURN(launch_gen_bf16(B, (uint64_t)n * k, seed ^ kSeedBXor, d->sm_count, s));
-  CU_OR_RETURN(cudaMemsetAsync(C, 0xFF, c_bytes, s));
+  CU_OR_RETURN(cudaMemsetAsync(C32, 0xFF, up(c32_bytes) + up(c16_bytes), s));  // NaN everywhere: an unwritten tile shows
   d->stats[GP_K_INIT].launches += 2;
-  for (uint32_t i = 0; i < warmup; ++i) CU_OR_RETURN(launch_gemm(plan, C, m, n, k, d->sm_count, s));
+  for (uint32_t i = 0; i < warmup; ++i) CU_OR_RETURN(launch_gemm(plan, out_bf16, Ctimed, m, n, k, d->sm_count, s));
   for (uint32_t i = 0; i < iters; ++i) {
     CU_OR_RETURN(cudaEventRecord(d->events[i], s));
-    CU_OR_RETURN(launch_gemm(plan, C, m, n, k, d->sm_count, s));
+    CU_OR_RETURN(launch_gemm(plan, out_bf16, Ctimed, m, n, k, d->sm_count, s));
   }
   CU_OR_RETURN(cudaEventRecord(d->events[iters], s));
+  // with bf16 output the strict checks run on the fp32 C of the same plan (one more launch, untimed), and the
+  // bf16 C must equal its rounding bit for bit
+  if (out_bf16) CU_OR_RETURN(launch_gemm(plan, false, C32, m, n, k, d->sm_count, s));
+  if (ctx->cfg.test_fault & GP_TEST_FAULT_GEMM_SKIP_TILE) {
+    const int tr = (int)(m / 256) - 1, tc = (int)((n / 256) / 2);
+    if (out_bf16) unwrite_tile_kernel<uint16_t><<<256, 256, 0, s>>>(C16, (int)n, tr * 256, tc * 256);
+    else unwrite_tile_kernel<float><<<256, 256, 0, s>>>(C32, (int)n, tr * 256, tc * 256);
+    CU_OR_RETURN(cudaGetLastError());
+  }
+  if (ctx->cfg.test_fault & GP_TEST_FAULT_GEMM_FLIP_BIT)  // one mantissa bit of one element of the timed C
+    CU_OR_RETURN(launch_bitflip(reinterpret_cast<uint64_t*>(Ctimed) + ((size_t)(m / 2) * n + n / 2) * (out_bf16 ? 2 : 4) / 8, 0, 3, s));
+  if (out_bf16) {
+    CU_OR_RETURN(cudaMemsetAsync(d->d_count, 0, sizeof(unsigned long long), s));
+    bf16_vs_f32_kernel<<<d->sm_count * 8, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(C16), reinterpret_cast<const float2*>(C32),
+                                                      (uint64_t)m * n / 2, d->d_count);
+    CU_OR_RETURN(cudaGetLastError());
+    CU_OR_RETURN(cudaMemcpyAsync(d->h_count, d->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+  }
 
-  // ---- checks: stratified samples (every 256x256 tile gets its share) + Freivalds ----
+  // ---- checks on the fp32 C: stratified samples (every 256x256 tile gets its share) + Freivalds ----
   std::vector<uint32_t> ij(2 * (size_t)samples);
   const uint32_t tm = m / 256, tn = n / 256, ntile = tm * tn;
   for (uint32_t t = 0; t < samples; ++t) {
@@ -727,10 +775,7 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   std::vector<float> got(samples);
   if (samples) {
     CU_OR_RETURN(cudaMemcpyAsync(d_ij, ij.data(), ij.size() * 4, cudaMemcpyHostToDevice, s));
-    if (out_bf16)
-      gather_kernel<uint16_t><<<(samples + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint16_t*>(C), (int)n, d_ij, (int)samples, d_sampled);
-    else
-      gather_kernel<float><<<(samples + 255) / 256, 256, 0, s>>>(C, (int)n, d_ij, (int)samples, d_sampled);
+    gather_kernel<float><<<(samples + 255) / 256, 256, 0, s>>>(C32, (int)n, d_ij, (int)samples, d_sampled);
     CU_OR_RETURN(cudaGetLastError());
     CU_OR_RETURN(cudaMemcpyAsync(got.data(), d_sampled, (size_t)samples * 4, cudaMemcpyDeviceToHost, s));
   }
@@ -738,18 +783,14 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   CU_OR_RETURN(cudaMemsetAsync(u, 0, 2 * vec_bytes, s));  // u and ub are adjacent
   fv_bt_x_kernel<<<dim3((k + 127) / 128, 32), 128, 0, s>>>(B, (int)n, (int)k, xs, u, ub);
   CU_OR_RETURN(cudaGetLastError());
-  if (out_bf16)
-    fv_rows_kernel<uint16_t><<<(m * 32 + 255) / 256, 256, 0, s>>>(A, reinterpret_cast<const uint16_t*>(C), (int)m, (int)n, (int)k, xs, u, ub, v, sc, w, cabs);
-  else
-    fv_rows_kernel<float><<<(m * 32 + 255) / 256, 256, 0, s>>>(A, C, (int)m, (int)n, (int)k, xs, u, ub, v, sc, w, cabs);
+  fv_rows_kernel<float><<<(m * 32 + 255) / 256, 256, 0, s>>>(A, C32, (int)m, (int)n, (int)k, xs, u, ub, v, sc, w, cabs);
   CU_OR_RETURN(cudaGetLastError());
-  std::vector<double> hv(m), hs(m), hw(m), hc(m);
-  CU_OR_RETURN(cudaMemcpyAsync(hc.data(), cabs, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
+  std::vector<double> hv(m), hs(m), hw(m);
   CU_OR_RETURN(cudaMemcpyAsync(hv.data(), v, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
   CU_OR_RETURN(cudaMemcpyAsync(hs.data(), sc, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
   CU_OR_RETURN(cudaMemcpyAsync(hw.data(), w, (size_t)m * 8, cudaMemcpyDeviceToHost, s));
-  CU_OR_RETURN(launch_pattern_verify(reinterpret_cast<uint64_t*>(C), c_bytes / 8, kPatNone, 0, d->scratch,
-                                     d->d_results, d->sm_count, s));
+  CU_OR_RETURN(launch_pattern_verify(reinterpret_cast<uint64_t*>(Ctimed), (out_bf16 ? c16_bytes : c32_bytes) / 8, kPatNone, 0,
+                                     d->scratch, d->d_results, d->sm_count, s));
   CU_OR_RETURN(cudaMemcpyAsync(d->h_results, d->d_results, sizeof(gp_pattern_result), cudaMemcpyDeviceToHost, s));
   CU_OR_RETURN(cudaStreamSynchronize(s));
 
@@ -769,16 +810,20 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   out->tflops_best = out->t.best_ms > 0 ? flop / (out->t.best_ms * 1e-3) / 1e12 : 0;
   out->tflops_median = out->t.median_ms > 0 ? flop / (out->t.median_ms * 1e-3) / 1e12 : 0;
   out->c_checksum = d->h_results[0].xor_;
+  if (out_bf16) out->bf16_mismatches = *d->h_count;
 
-  // host reference of the sampled entries: fp64 dot products of the bf16-rounded generator output
+  // host reference of the sampled entries: fp64 dot products of the bf16-rounded generator output.
+  // Anything that is not a finite number is an error outright (C was pre-filled with NaN bit patterns, so an
+  // unwritten tile reads as NaN; std::max and comparisons silently drop NaN, hence the explicit test first).
   const double tol = ctx->cfg.gemm_tol > 0 ? ctx->cfg.gemm_tol : 1e-3;
-  const double out_round = out_bf16 ? 1.0 / 256.0 : 0.0;
+  const double kBad = 1e30;
   std::vector<double> err(samples, 0.0);
   const unsigned nthreads = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
   std::vector<std::thread> th;
   for (unsigned w0 = 0; w0 < nthreads; ++w0) {
     th.emplace_back([&, w0] {
       for (uint32_t t = w0; t < samples; t += nthreads) {
+        if (!std::isfinite(got[t])) { err[t] = kBad; continue; }
         const uint64_t i = ij[2 * t], j = ij[2 * t + 1];
         double acc = 0, aacc = 0;
         for (uint32_t kk = 0; kk < k; ++kk) {
@@ -787,24 +832,25 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
           acc += x * y;
           aacc += fabs(x * y);
         }
-        // a bf16 result may differ from the exact value by its own rounding, 2^-8 |ref| at most
-        const double e = std::max(0.0, fabs((double)got[t] - acc) - out_round * fabs(acc));
-        err[t] = (std::isfinite((double)got[t]) && aacc > 0) ? e / aacc : (e == 0 ? 0.0 : 1e30);
+        const double e = fabs((double)got[t] - acc);
+        err[t] = aacc > 0 ? e / aacc : (e == 0 ? 0.0 : kBad);
       }
     });
   }
   for (auto& t : th) t.join();
   out->samples = samples;
   for (uint32_t t = 0; t < samples; ++t) {
-    out->max_scaled_err = std::max(out->max_scaled_err, err[t]);
+    if (!(err[t] <= out->max_scaled_err)) out->max_scaled_err = err[t];  // also true for NaN
     if (!(err[t] <= tol)) out->samples_bad++;
   }
   for (uint32_t i = 0; i < m; ++i) {
-    const double e = std::max(0.0, fabs(hw[i] - hv[i]) - out_round * hc[i]);
-    const double r = (std::isfinite(hw[i]) && hs[i] > 0) ? e / hs[i] : (e == 0 ? 0.0 : 1e30);
-    out->freivalds_err = std::max(out->freivalds_err, r);
+    double r;
+    if (!std::isfinite(hw[i]) || !std::isfinite(hv[i]) || !std::isfinite(hs[i])) r = kBad;
+    else { const double e = fabs(hw[i] - hv[i]); r = hs[i] > 0 ? e / hs[i] : (e == 0 ? 0.0 : kBad); }
+    if (!(r <= out->freivalds_err)) out->freivalds_err = r;
   }
   if (!(out->freivalds_err <= tol)) out->samples_bad++;
+  if (out->bf16_mismatches) out->samples_bad += (uint32_t)std::min<uint64_t>(out->bf16_mismatches, 1u << 30);
   return GP_OK;
 }
 

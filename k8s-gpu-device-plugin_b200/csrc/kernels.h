@@ -32,6 +32,10 @@ cudaError_t launch_verify_scratch_init(void* scratch, cudaStream_t stream);
 cudaError_t launch_pattern_verify(const uint64_t* words, uint64_t nwords, int kind, int pass,
                                   void* scratch, gp_pattern_result* d_result, int sm_count,
                                   cudaStream_t stream);
+// fold the accumulator slots of `scratch` into *d_result (sum, xor, wsum as accumulated; mismatches as
+// accumulated) and return the slots to their rest state: the one-CTA finalize alone, for kernels that fill
+// the slots themselves (the P2P read kernels)
+cudaError_t launch_verify_fold(void* scratch, gp_pattern_result* d_result, cudaStream_t stream);
 cudaError_t launch_bitflip(uint64_t* words, uint64_t word_index, int bit, cudaStream_t stream);
 
 // HBM stream kernels.  bytes is a multiple of 1 MiB; variant is GP_STREAM_VEC or GP_STREAM_TMA.

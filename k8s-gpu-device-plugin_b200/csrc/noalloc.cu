@@ -39,6 +39,13 @@ bool kind_pass_ok(int kind, int pass) {
 
 }  // namespace
 
+// A cudaDeviceReset destroys the device's copy of the array; the address cached for it is then stale.
+// gp_device_reset calls this; a caller that resets the device itself cannot, see include/gpuprobe.h.
+void gp::noalloc_forget_device(int ordinal) {
+  std::lock_guard<std::mutex> g(g_setup_mu);
+  if (ordinal >= 0 && ordinal < kMaxOrdinals) g_scratch_addr[ordinal] = nullptr;
+}
+
 extern "C" int gp_pattern_verify_noalloc(int device_ordinal, const uint64_t* d_words, uint64_t nwords,
                                          int kind, int pass, gp_pattern_result* d_result, void* stream) {
   using namespace gp;
@@ -48,6 +55,13 @@ extern "C" int gp_pattern_verify_noalloc(int device_ordinal, const uint64_t* d_w
   }
   if (!d_result || (!d_words && nwords) || !kind_pass_ok(kind, pass) || (nwords % 64)) {
     set_error("gp_pattern_verify_noalloc: null pointer, bad kind/pass, or nwords not a multiple of 64");
+    return GP_ERR_INVALID;
+  }
+  // The kernels read 256 bits at a time and the result is written as six 64-bit words.  A misaligned
+  // pointer would not fail here but inside the kernel, as a sticky fault that takes the caller's whole
+  // context with it, so it is refused up front.
+  if ((reinterpret_cast<uintptr_t>(d_words) & 31u) || (reinterpret_cast<uintptr_t>(d_result) & 7u)) {
+    set_error("gp_pattern_verify_noalloc: d_words must be 32-byte aligned and d_result 8-byte aligned");
     return GP_ERR_INVALID;
   }
   if (nwords > GP_NOALLOC_MAX_WORDS) {

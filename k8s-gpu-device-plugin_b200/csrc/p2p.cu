@@ -18,6 +18,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -28,6 +29,23 @@
 
 namespace gp {
 
+// accumulate what a peer read loaded: sum and xor of the u64 words, folded per warp into the verify
+// scratch slots (pattern.cu) with fire-and-forget reductions; launch_verify_fold turns the slots into a
+// gp_pattern_result the host compares with the closed form of the pattern the peer holds
+__device__ __forceinline__ void p2p_fold(VerifySlot* __restrict__ slots, uint64_t sum, uint64_t xr) {
+  sum = warp_sum_u64(sum);
+  xr = warp_xor_u64(xr);
+  if ((threadIdx.x & 31) == 0) {
+    VerifySlot* s = slots + ((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) & (kVerifySlots - 1));
+    atomicAdd(reinterpret_cast<unsigned long long*>(&s->sum), (unsigned long long)sum);
+    atomicXor(reinterpret_cast<unsigned long long*>(&s->xor_), (unsigned long long)xr);
+  }
+}
+__device__ __forceinline__ void p2p_acc(const u64x4& x, uint64_t& sum, uint64_t& xr) {
+  sum += (x.v[0] + x.v[1]) + (x.v[2] + x.v[3]);
+  xr ^= (x.v[0] ^ x.v[1]) ^ (x.v[2] ^ x.v[3]);
+}
+
 #define CU_OR_RETURN(call)                                               \
   do {                                                                   \
     cudaError_t e__ = (call);                                            \
@@ -37,24 +55,24 @@ namespace gp {
 constexpr int kP2PThreads = 512;
 constexpr int kP2PUnroll = 4;  // 4 x 32 B in flight per thread: peer latency is ~2-4k cycles
 
-// kernel on `src`: read every vector of the peer buffer, fold into a value nobody stores
+// kernel on `src`: read every vector of the peer buffer and fold it (sum, xor) for the host to check
 __global__ void __launch_bounds__(kP2PThreads)
-p2p_read_kernel(const u64x4* __restrict__ peer, uint64_t nvec, unsigned long long* __restrict__ sink) {
+p2p_read_kernel(const u64x4* __restrict__ peer, uint64_t nvec, VerifySlot* __restrict__ slots) {
   const uint64_t stride = (uint64_t)gridDim.x * kP2PThreads;
   uint64_t g = (uint64_t)blockIdx.x * kP2PThreads + threadIdx.x;
-  uint64_t acc = 0;
+  uint64_t sum = 0, xr = 0;
   for (; g + (kP2PUnroll - 1) * stride < nvec; g += kP2PUnroll * stride) {
     u64x4 v[kP2PUnroll];
 #pragma unroll
     for (int u = 0; u < kP2PUnroll; ++u) v[u] = ld256_stream(peer + g + u * stride);
 #pragma unroll
-    for (int u = 0; u < kP2PUnroll; ++u) acc += (v[u].v[0] ^ v[u].v[1]) + (v[u].v[2] ^ v[u].v[3]);
+    for (int u = 0; u < kP2PUnroll; ++u) p2p_acc(v[u], sum, xr);
   }
   for (; g < nvec; g += stride) {
     const u64x4 v = ld256_stream(peer + g);
-    acc += (v.v[0] ^ v.v[1]) + (v.v[2] ^ v.v[3]);
+    p2p_acc(v, sum, xr);
   }
-  if (acc == 0x9E3779B97F4A7C15ull) atomicAdd(sink, 1ull);  // keeps the loads alive
+  p2p_fold(slots, sum, xr);
 }
 
 // kernel on `src`: store the address pattern into the peer buffer
@@ -71,9 +89,9 @@ p2p_write_kernel(u64x4* __restrict__ peer, uint64_t nvec, uint64_t tag) {
 // non-persistent shapes: one CTA per contiguous chunk (kP2PThreads x U vectors), no loop
 template <int U>
 __global__ void __launch_bounds__(kP2PThreads)
-p2p_read_np_kernel(const u64x4* __restrict__ peer, uint64_t nvec, unsigned long long* __restrict__ sink) {
+p2p_read_np_kernel(const u64x4* __restrict__ peer, uint64_t nvec, VerifySlot* __restrict__ slots) {
   const uint64_t g0 = (uint64_t)blockIdx.x * (kP2PThreads * U) + threadIdx.x;
-  uint64_t acc = 0;
+  uint64_t sum = 0, xr = 0;
   u64x4 v[U];
 #pragma unroll
   for (int u = 0; u < U; ++u) {
@@ -81,8 +99,8 @@ p2p_read_np_kernel(const u64x4* __restrict__ peer, uint64_t nvec, unsigned long 
     if (g < nvec) v[u] = ld256_stream(peer + g); else v[u] = u64x4{{0, 0, 0, 0}};
   }
 #pragma unroll
-  for (int u = 0; u < U; ++u) acc += (v[u].v[0] ^ v[u].v[1]) + (v[u].v[2] ^ v[u].v[3]);
-  if (acc == 0x9E3779B97F4A7C15ull) atomicAdd(sink, 1ull);
+  for (int u = 0; u < U; ++u) p2p_acc(v[u], sum, xr);
+  p2p_fold(slots, sum, xr);
 }
 template <int U>
 __global__ void __launch_bounds__(kP2PThreads)
@@ -106,25 +124,25 @@ struct PeerTable {
   int n;
 };
 __global__ void __launch_bounds__(kP2PThreads)
-p2p_read_all_kernel(PeerTable t, uint64_t nvec_per_peer, unsigned long long* __restrict__ sink) {
+p2p_read_all_kernel(PeerTable t, uint64_t nvec_per_peer, VerifySlot* __restrict__ slots) {
   const int peer = blockIdx.x % t.n;
   const uint64_t cta = blockIdx.x / t.n, ctas = gridDim.x / t.n;
   const u64x4* __restrict__ base = t.p[peer];
   const uint64_t stride = ctas * kP2PThreads;
-  uint64_t acc = 0;
+  uint64_t sum = 0, xr = 0;
   uint64_t g = cta * kP2PThreads + threadIdx.x;
   for (; g + (kP2PUnroll - 1) * stride < nvec_per_peer; g += kP2PUnroll * stride) {
     u64x4 v[kP2PUnroll];
 #pragma unroll
     for (int u = 0; u < kP2PUnroll; ++u) v[u] = ld256_stream(base + g + u * stride);
 #pragma unroll
-    for (int u = 0; u < kP2PUnroll; ++u) acc += (v[u].v[0] ^ v[u].v[1]) + (v[u].v[2] ^ v[u].v[3]);
+    for (int u = 0; u < kP2PUnroll; ++u) p2p_acc(v[u], sum, xr);
   }
   for (; g < nvec_per_peer; g += stride) {
     const u64x4 v = ld256_stream(base + g);
-    acc += (v.v[0] ^ v.v[1]) + (v.v[2] ^ v.v[3]);
+    p2p_acc(v, sum, xr);
   }
-  if (acc == 0x9E3779B97F4A7C15ull) atomicAdd(sink, 1ull);
+  p2p_fold(slots, sum, xr);
 }
 
 // peer write through TMA: threads build a 16 KiB tile of the pattern in shared memory, one
@@ -194,12 +212,32 @@ struct Xfer {
   int src, dst;
 };
 
-// run a set of transfers concurrently (one per src device), return best-of-iters GB/s of each
-static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, bool write, int iters,
-                     std::vector<double>* gbps_out) {
+enum XferMode { kXferRead = 0, kXferWrite = 1, kXferCopyEngine = 2 };
+
+// SUM and XOR of the address pattern (pass 0) over n words: SURVEY.md §8(c) closed forms
+static void address_closed_form(uint64_t n, uint64_t* sum, uint64_t* xr) {
+  *sum = 4 * n * (n - 1);  // mod 2^64 by construction
+  const uint64_t m = n - 1;
+  const uint64_t X[4] = {m, 1, m + 1, 0};
+  *xr = n ? 8 * X[m & 3] : 0;
+}
+
+struct P2PState {
+  bool data_bad = false;  // a read returned the wrong bytes, or a write / copy did not land intact
+};
+
+// run a set of transfers concurrently (one per src device), return best-of-iters GB/s of each.
+// Reads fold what they loaded into the src device's verify slots; the fold lands in d_results[it] and
+// is compared with the closed form after the sync.
+static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, XferMode mode, int iters,
+                     std::vector<double>* gbps_out, P2PState* st) {
   const uint64_t nvec = bytes / 32;
   gbps_out->assign(xs.size(), 0.0);
   std::vector<float> best(xs.size(), 1e30f);
+  // launch shape: measured on 2 and 8 x B200 (tools/p2p_shapes.py, profiles/multi_gpu_8_r01.json): read
+  // 776-785 GB/s and write 713 GB/s per direction at 1 GiB for EVERY shape tried — the link protocol, not
+  // the kernel, is the limit — so the default is the non-persistent shape the local kernels use
+  static const int shape = GP_DEV_SWITCH("GPUPROBE_P2P_SHAPE", 1);
   for (int it = 0; it < iters + 1; ++it) {  // first pass is the warm-up
     for (size_t i = 0; i < xs.size(); ++i) {
       Device* s = ctx->devs[(size_t)xs[i].src].get();
@@ -208,12 +246,12 @@ static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, bool w
       CU_OR_RETURN(cudaEventRecord(s->events[0], s->stream));
       const uint64_t tag = 0xC0DE0000ull + (uint64_t)xs[i].src;
       u64x4* pa = reinterpret_cast<u64x4*>(d->arena);
-      // Measured on 2 x B200 (tools/p2p_shapes.py): read 776-785 GB/s and write 713 GB/s per direction at
-      // 1 GiB for EVERY launch shape tried — the link protocol, not the kernel, is the limit — so the
-      // default is the non-persistent shape the local kernels use; the others stay for experiments.
-      static const int shape = getenv("GPUPROBE_P2P_SHAPE") ? atoi(getenv("GPUPROBE_P2P_SHAPE")) : 1;
+      VerifySlot* slots = reinterpret_cast<VerifySlot*>(s->scratch);
       auto npgrid = [&](int U) { return (unsigned)((nvec + (uint64_t)kP2PThreads * U - 1) / ((uint64_t)kP2PThreads * U)); };
-      if (write) {
+      if (mode == kXferCopyEngine) {
+        // the yardstick: the driver's own peer copy, src's source half -> dst's landing half
+        CU_OR_RETURN(cudaMemcpyPeerAsync(d->arena + bytes, d->ordinal, s->arena, s->ordinal, bytes, s->stream));
+      } else if (mode == kXferWrite) {
         if (shape == 1) p2p_write_np_kernel<1><<<npgrid(1), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
         else if (shape == 2) p2p_write_np_kernel<4><<<npgrid(4), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
         else if (shape == 3) p2p_write_kernel<<<s->sm_count * 2, kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
@@ -222,14 +260,15 @@ static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, bool w
           p2p_write_tma_kernel<<<s->sm_count * 4, 128, 0, s->stream>>>(reinterpret_cast<uint8_t*>(pa), bytes / kP2PTile, tag);
         else p2p_write_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(pa, nvec, tag);
       } else {
-        if (shape == 1) p2p_read_np_kernel<2><<<npgrid(2), kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
-        else if (shape == 2) p2p_read_np_kernel<8><<<npgrid(8), kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
-        else if (shape == 3) p2p_read_kernel<<<s->sm_count * 2, kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
-        else if (shape == 4) p2p_read_kernel<<<s->sm_count, kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
-        else p2p_read_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(pa, nvec, s->d_count);
+        if (shape == 1) p2p_read_np_kernel<2><<<npgrid(2), kP2PThreads, 0, s->stream>>>(pa, nvec, slots);
+        else if (shape == 2) p2p_read_np_kernel<8><<<npgrid(8), kP2PThreads, 0, s->stream>>>(pa, nvec, slots);
+        else if (shape == 3) p2p_read_kernel<<<s->sm_count * 2, kP2PThreads, 0, s->stream>>>(pa, nvec, slots);
+        else if (shape == 4) p2p_read_kernel<<<s->sm_count, kP2PThreads, 0, s->stream>>>(pa, nvec, slots);
+        else p2p_read_kernel<<<p2p_grid(nvec, s->sm_count), kP2PThreads, 0, s->stream>>>(pa, nvec, slots);
       }
       CU_OR_RETURN(cudaGetLastError());
       CU_OR_RETURN(cudaEventRecord(s->events[1], s->stream));
+      if (mode == kXferRead) CU_OR_RETURN(launch_verify_fold(s->scratch, s->d_results + it, s->stream));
     }
     for (size_t i = 0; i < xs.size(); ++i) {
       Device* s = ctx->devs[(size_t)xs[i].src].get();
@@ -245,25 +284,44 @@ static int run_xfers(Ctx* ctx, const std::vector<Xfer>& xs, size_t bytes, bool w
       }
     }
   }
+  if (mode == kXferRead) {
+    uint64_t esum, exor;
+    address_closed_form(bytes / 8, &esum, &exor);
+    for (size_t i = 0; i < xs.size(); ++i) {
+      Device* s = ctx->devs[(size_t)xs[i].src].get();
+      CU_OR_RETURN(cudaSetDevice(s->ordinal));
+      CU_OR_RETURN(cudaMemcpy(s->h_results, s->d_results, (size_t)(iters + 1) * sizeof(gp_pattern_result), cudaMemcpyDeviceToHost));
+      for (int it = 0; it < iters + 1; ++it)
+        if (s->h_results[it].sum != esum || s->h_results[it].xor_ != exor) {
+          set_error("device %d read the wrong bytes from device %d: sum %016llx xor %016llx, expected %016llx %016llx",
+                    xs[i].src, xs[i].dst, (unsigned long long)s->h_results[it].sum, (unsigned long long)s->h_results[it].xor_,
+                    (unsigned long long)esum, (unsigned long long)exor);
+          st->data_bad = true;
+          return GP_ERR_CUDA;
+        }
+    }
+  }
   for (size_t i = 0; i < xs.size(); ++i) (*gbps_out)[i] = (double)bytes / (best[i] * 1e-3) / 1e9;
   return GP_OK;
 }
 
-int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
-  if (ngpus > (int)ctx->devs.size()) { set_error("ngpus %d > visible %zu", ngpus, ctx->devs.size()); return GP_ERR_NO_DEVICE; }
+// multi_mu and every device lock held by the caller
+static int p2p_probe_locked(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps, P2PState* st, bool keep) {
   if (bytes == 0 || bytes % 32) { set_error("bytes must be a non-zero multiple of 32"); return GP_ERR_INVALID; }
-  std::lock_guard<std::mutex> multi(ctx->multi_mu);
-  std::vector<std::unique_lock<std::mutex>> locks;
-  for (int i = 0; i < ngpus; ++i) locks.emplace_back(ctx->devs[(size_t)i]->mu);  // ordinal order: no deadlock
+  const bool copy_engine = dir == GP_P2P_COPY_ENGINE || dir == GP_P2P_COPY_ENGINE_BIDIR;
   for (int i = 0; i < ngpus * ngpus; ++i) gbps[i] = 0.0;
+  unsigned long long all_mask = 0;
+  for (int i = 0; i < ngpus; ++i) all_mask |= 1ull << ctx->devs[(size_t)i]->ordinal;
   for (int i = 0; i < ngpus; ++i) {
     Device* d = ctx->devs[(size_t)i].get();
     int rc = device_prepare(ctx, d);
     if (rc) return rc;
-    rc = ensure_arena(ctx, d, std::max<size_t>(bytes, 1 << 20));
+    rc = ensure_arena(ctx, d, std::max<size_t>((copy_engine ? 2 : 1) * bytes, 1 << 20));
     if (rc) return rc;
     d->triad_operands_bytes = 0;
-    CU_OR_RETURN(cudaMemsetAsync(d->arena, 0x5A, bytes, d->stream));
+    // what every reader must find: the address pattern, word index from the arena base
+    CU_OR_RETURN(launch_pattern_fill(reinterpret_cast<uint64_t*>(d->arena), bytes / 8, GP_PAT_ADDRESS, 0, d->sm_count, d->stream));
+    if (copy_engine) CU_OR_RETURN(cudaMemsetAsync(d->arena + bytes, 0x5A, bytes, d->stream));
     CU_OR_RETURN(cudaMemsetAsync(d->d_count, 0, sizeof(unsigned long long), d->stream));
     CU_OR_RETURN(cudaStreamSynchronize(d->stream));
   }
@@ -279,13 +337,24 @@ int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
       (void)cudaGetLastError();
     }
   }
-  if (dir == 3) {
+  // a VMM arena is not covered by cudaDeviceEnablePeerAccess: grant the peers explicitly
+  for (int i = 0; i < ngpus; ++i) {
+    int rc = arena_grant_peers(ctx->devs[(size_t)i].get(), all_mask);
+    if (rc) return rc;
+  }
+  auto done = [&](int rc) {
+    if (!keep)
+      for (int i = 0; i < ngpus; ++i) free_arena(ctx->devs[(size_t)i].get());
+    return rc;
+  };
+  if (dir == GP_P2P_ALL_AT_ONCE) {
     // every GPU reads `bytes` from each of its n-1 peers at once; row i holds GPU i's aggregate
     // ingress divided evenly over its peers, the diagonal holds the aggregate itself
-    if (ngpus < 2 || ngpus > 9) { set_error("all-at-once mode needs 2..9 GPUs"); return GP_ERR_INVALID; }
+    if (ngpus < 2 || ngpus > 9) { set_error("all-at-once mode needs 2..9 GPUs"); return done(GP_ERR_INVALID); }
     const uint64_t nvec = bytes / 32;
+    const int kIt = 4;
     std::vector<float> best((size_t)ngpus, 1e30f);
-    for (int it = 0; it < 4; ++it) {
+    for (int it = 0; it < kIt; ++it) {
       for (int i = 0; i < ngpus; ++i) {
         Device* s = ctx->devs[(size_t)i].get();
         PeerTable t{};
@@ -294,9 +363,10 @@ int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
         CU_OR_RETURN(cudaSetDevice(i));
         CU_OR_RETURN(cudaEventRecord(s->events[0], s->stream));
         const int ctas_per_peer = std::max(1, s->sm_count * 4 / t.n);
-        p2p_read_all_kernel<<<ctas_per_peer * t.n, kP2PThreads, 0, s->stream>>>(t, nvec, s->d_count);
+        p2p_read_all_kernel<<<ctas_per_peer * t.n, kP2PThreads, 0, s->stream>>>(t, nvec, reinterpret_cast<VerifySlot*>(s->scratch));
         CU_OR_RETURN(cudaGetLastError());
         CU_OR_RETURN(cudaEventRecord(s->events[1], s->stream));
+        CU_OR_RETURN(launch_verify_fold(s->scratch, s->d_results + it, s->stream));
       }
       for (int i = 0; i < ngpus; ++i) {
         Device* s = ctx->devs[(size_t)i].get();
@@ -312,38 +382,53 @@ int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
         }
       }
     }
+    uint64_t esum, exor;
+    address_closed_form(bytes / 8, &esum, &exor);
+    esum *= (uint64_t)(ngpus - 1);
+    if (!((ngpus - 1) & 1)) exor = 0;
+    for (int i = 0; i < ngpus; ++i) {
+      Device* s = ctx->devs[(size_t)i].get();
+      CU_OR_RETURN(cudaSetDevice(i));
+      CU_OR_RETURN(cudaMemcpy(s->h_results, s->d_results, kIt * sizeof(gp_pattern_result), cudaMemcpyDeviceToHost));
+      for (int it = 0; it < kIt; ++it)
+        if (s->h_results[it].sum != esum || s->h_results[it].xor_ != exor) {
+          set_error("device %d read the wrong bytes from its peers in the all-at-once round", i);
+          st->data_bad = true;
+          return done(GP_ERR_CUDA);
+        }
+    }
     for (int i = 0; i < ngpus; ++i) {
       const double agg = (double)bytes * (ngpus - 1) / (best[(size_t)i] * 1e-3) / 1e9;
       for (int j = 0; j < ngpus; ++j) gbps[i * ngpus + j] = i == j ? agg : agg / (ngpus - 1);
     }
-    if (!ctx->cfg.keep_arena)
-      for (int i = 0; i < ngpus; ++i) free_arena(ctx->devs[(size_t)i].get());
-    return GP_OK;
+    return done(GP_OK);
   }
-  const bool write = dir == 1 || dir == 2;
+  const bool write = dir == GP_P2P_WRITE || dir == GP_P2P_BIDIR_WRITE;
+  const bool bidir = dir == GP_P2P_BIDIR_WRITE || dir == GP_P2P_BIDIR_READ || dir == GP_P2P_COPY_ENGINE_BIDIR;
+  const XferMode mode = copy_engine ? kXferCopyEngine : (write ? kXferWrite : kXferRead);
   const int iters = 3;
   std::vector<double> r;
-  // diagonal: the same kernel on local memory, all GPUs at once
+  // diagonal: the same transfer on local memory, all GPUs at once
   {
     std::vector<Xfer> xs;
     for (int i = 0; i < ngpus; ++i) xs.push_back({i, i});
-    int rc = run_xfers(ctx, xs, bytes, write, iters, &r);
-    if (rc) return rc;
+    int rc = run_xfers(ctx, xs, bytes, mode, iters, &r, st);
+    if (rc) return done(rc);
     for (int i = 0; i < ngpus; ++i) gbps[i * ngpus + i] = r[(size_t)i];
   }
   for (const auto& round : rounds_for(ngpus)) {
-    if (dir == 2 || dir == 4) {  // both directions of every pair at once: 2 = writes, 4 = reads
+    if (bidir) {  // both directions of every pair at once
       std::vector<Xfer> xs;
       for (auto pr : round) { xs.push_back({pr.first, pr.second}); xs.push_back({pr.second, pr.first}); }
-      int rc = run_xfers(ctx, xs, bytes, dir == 2, iters, &r);
-      if (rc) return rc;
+      int rc = run_xfers(ctx, xs, bytes, mode, iters, &r, st);
+      if (rc) return done(rc);
       for (size_t i = 0; i < xs.size(); ++i) gbps[xs[i].src * ngpus + xs[i].dst] = r[i];
     } else {
       for (int phase = 0; phase < 2; ++phase) {
         std::vector<Xfer> xs;
         for (auto pr : round) xs.push_back(phase == 0 ? Xfer{pr.first, pr.second} : Xfer{pr.second, pr.first});
-        int rc = run_xfers(ctx, xs, bytes, write, iters, &r);
-        if (rc) return rc;
+        int rc = run_xfers(ctx, xs, bytes, mode, iters, &r, st);
+        if (rc) return done(rc);
         for (size_t i = 0; i < xs.size(); ++i) gbps[xs[i].src * ngpus + xs[i].dst] = r[i];
       }
     }
@@ -364,12 +449,45 @@ int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
       CU_OR_RETURN(cudaGetLastError());
       CU_OR_RETURN(cudaMemcpyAsync(d->h_count, d->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, d->stream));
       CU_OR_RETURN(cudaStreamSynchronize(d->stream));
-      if (*d->h_count) { set_error("peer writes into device %d did not land intact (%llu bad vectors)", i, *d->h_count); return GP_ERR_CUDA; }
+      if (*d->h_count) {
+        set_error("peer writes into device %d did not land intact (%llu bad vectors)", i, *d->h_count);
+        st->data_bad = true;
+        return done(GP_ERR_CUDA);
+      }
     }
   }
-  if (!ctx->cfg.keep_arena)
-    for (int i = 0; i < ngpus; ++i) free_arena(ctx->devs[(size_t)i].get());
-  return GP_OK;
+  // a peer copy must have landed too: every landing half must verify as the address pattern of its source
+  if (copy_engine) {
+    for (int i = 0; i < ngpus; ++i) {
+      Device* d = ctx->devs[(size_t)i].get();
+      CU_OR_RETURN(cudaSetDevice(i));
+      CU_OR_RETURN(launch_pattern_verify(reinterpret_cast<const uint64_t*>(d->arena + bytes), bytes / 8, GP_PAT_ADDRESS, 0,
+                                         d->scratch, d->d_results, d->sm_count, d->stream));
+      CU_OR_RETURN(cudaMemcpyAsync(d->h_results, d->d_results, sizeof(gp_pattern_result), cudaMemcpyDeviceToHost, d->stream));
+      CU_OR_RETURN(cudaStreamSynchronize(d->stream));
+      if (d->h_results[0].mismatches) {
+        set_error("peer copies into device %d did not land intact (%llu bad words)", i, (unsigned long long)d->h_results[0].mismatches);
+        st->data_bad = true;
+        return done(GP_ERR_CUDA);
+      }
+    }
+  }
+  return done(GP_OK);
+}
+
+struct MultiLock {
+  std::lock_guard<std::mutex> multi;
+  std::vector<std::unique_lock<std::mutex>> locks;
+  MultiLock(Ctx* ctx, int n) : multi(ctx->multi_mu) {
+    for (int i = 0; i < n; ++i) locks.emplace_back(ctx->devs[(size_t)i]->mu);  // ordinal order: no deadlock
+  }
+};
+
+int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps) {
+  if (ngpus > (int)ctx->devs.size()) { set_error("ngpus %d > visible %zu", ngpus, ctx->devs.size()); return GP_ERR_NO_DEVICE; }
+  MultiLock L(ctx, ngpus);
+  P2PState st;
+  return p2p_probe_locked(ctx, ngpus, bytes, dir, gbps, &st, ctx->cfg.keep_arena != 0);
 }
 
 // ------------------------------------------------------------------ NCCL ----
@@ -390,7 +508,7 @@ static NcclApi* nccl_api(Ctx* ctx) {
   // end up with a second copy under the same soname); otherwise the system one, or the path in
   // GPUPROBE_NCCL_LIB.
   void* h = nullptr;
-  if (const char* path = getenv("GPUPROBE_NCCL_LIB")) h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+  if (const char* path = getenv("GPUPROBE_NCCL_LIB")) h = dlopen(path, RTLD_NOW | RTLD_LOCAL);  // the one environment variable of a release build
   if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
   if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
   if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
@@ -435,15 +553,11 @@ __global__ void fill_f32_kernel(float* p, uint64_t n, float v) {
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
 }
 
-int allreduce_probe(Ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters, double* algbw,
-                    double* busbw) {
-  if (nranks > (int)ctx->devs.size()) { set_error("nranks %d > visible %zu", nranks, ctx->devs.size()); return GP_ERR_NO_DEVICE; }
+static int allreduce_probe_locked(Ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters, double* algbw,
+                                  double* busbw, bool keep) {
   if (bytes == 0 || bytes % 4) { set_error("bytes must be a non-zero multiple of 4"); return GP_ERR_INVALID; }
-  std::lock_guard<std::mutex> multi(ctx->multi_mu);
   NcclApi* api = nccl_api(ctx);
   if (!api) return GP_ERR_NCCL;
-  std::vector<std::unique_lock<std::mutex>> locks;
-  for (int i = 0; i < nranks; ++i) locks.emplace_back(ctx->devs[(size_t)i]->mu);
   const uint64_t count = bytes / 4;
   for (int i = 0; i < nranks; ++i) {
     Device* d = ctx->devs[(size_t)i].get();
@@ -515,8 +629,75 @@ int allreduce_probe(Ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_
   const double alg = (double)bytes / t / 1e9;
   if (algbw) *algbw = alg;
   if (busbw) *busbw = alg * 2.0 * (nranks - 1) / nranks;
-  if (!ctx->cfg.keep_arena)
+  if (!keep)
     for (int i = 0; i < nranks; ++i) free_arena(ctx->devs[(size_t)i].get());
+  return GP_OK;
+}
+
+int allreduce_probe(Ctx* ctx, int nranks, size_t bytes, uint32_t warmup, uint32_t iters, double* algbw,
+                    double* busbw) {
+  if (nranks > (int)ctx->devs.size()) { set_error("nranks %d > visible %zu", nranks, ctx->devs.size()); return GP_ERR_NO_DEVICE; }
+  MultiLock L(ctx, nranks);
+  return allreduce_probe_locked(ctx, nranks, bytes, warmup, iters, algbw, busbw, ctx->cfg.keep_arena != 0);
+}
+
+// The fabric verdict: read and write matrices, their spread and worst pair, the all-reduce, graded against
+// gp_config's floors.  A transfer that returns or lands the wrong bytes makes the verdict unhealthy (data_ok = 0)
+// instead of failing the call: the caller gets the matrices measured so far and the reason in failed.
+int fabric_probe(Ctx* ctx, int ngpus, gp_fabric_result* out) {
+  const auto t0 = std::chrono::steady_clock::now();
+  memset(out, 0, sizeof(*out));
+  out->struct_size = (uint32_t)sizeof(*out);
+  out->ngpus = (uint32_t)ngpus;
+  out->worst_src = out->worst_dst = -1;
+  out->data_ok = 1;
+  if (ngpus > (int)ctx->devs.size()) { set_error("ngpus %d > visible %zu", ngpus, ctx->devs.size()); return GP_ERR_NO_DEVICE; }
+  const size_t bytes = ctx->cfg.fabric_bytes ? (size_t)ctx->cfg.fabric_bytes : ((size_t)1 << 30);
+  out->bytes = bytes;
+  MultiLock L(ctx, ngpus);
+  P2PState st;
+  int rc = p2p_probe_locked(ctx, ngpus, bytes, GP_P2P_READ, out->read_gbps, &st, /*keep=*/true);
+  if (rc == GP_OK) rc = p2p_probe_locked(ctx, ngpus, bytes, GP_P2P_WRITE, out->write_gbps, &st, /*keep=*/true);
+  if (rc != GP_OK && !st.data_bad) {
+    for (int i = 0; i < ngpus; ++i) if (!ctx->cfg.keep_arena) free_arena(ctx->devs[(size_t)i].get());
+    return rc;
+  }
+  if (st.data_bad) { out->data_ok = 0; out->failed |= 8u; }
+  auto stats = [&](const double* m, double* mn, double* mx, double* mean) {
+    double lo = 1e300, hi = 0, sum = 0;
+    int cnt = 0;
+    for (int i = 0; i < ngpus; ++i)
+      for (int j = 0; j < ngpus; ++j) {
+        if (i == j) continue;
+        const double v = m[i * ngpus + j];
+        lo = std::min(lo, v); hi = std::max(hi, v); sum += v; ++cnt;
+        if (out->worst_src < 0 || v < out->worst_gbps) { out->worst_gbps = v; out->worst_src = i; out->worst_dst = j; }
+      }
+    *mn = cnt ? lo : 0; *mx = hi; *mean = cnt ? sum / cnt : 0;
+  };
+  stats(out->read_gbps, &out->read_min, &out->read_max, &out->read_mean);
+  stats(out->write_gbps, &out->write_min, &out->write_max, &out->write_mean);
+  if (ngpus >= 2) {
+    const double sr = out->read_min > 0 ? out->read_max / out->read_min : 1e30;
+    const double sw = out->write_min > 0 ? out->write_max / out->write_min : 1e30;
+    out->spread = out->data_ok ? std::max(sr, sw) : 0.0;
+    if (out->data_ok) {
+      if (ctx->cfg.min_p2p_gbps > 0 && out->worst_gbps < ctx->cfg.min_p2p_gbps) out->failed |= 1u;
+      if (ctx->cfg.max_p2p_spread > 0 && out->spread > ctx->cfg.max_p2p_spread) out->failed |= 2u;
+    }
+    rc = allreduce_probe_locked(ctx, ngpus, bytes, 2, 5, &out->allreduce_algbw_gbps, &out->allreduce_busbw_gbps, /*keep=*/true);
+    out->allreduce_error = rc;
+    // NCCL not installed is "not measured", not a fabric fault; a failing or slow all-reduce is
+    if (rc != GP_OK && rc != GP_ERR_NCCL) out->failed |= 4u;
+    if (rc == GP_OK && ctx->cfg.min_allreduce_busbw_gbps > 0 && out->allreduce_busbw_gbps < ctx->cfg.min_allreduce_busbw_gbps)
+      out->failed |= 4u;
+  } else {
+    out->spread = 1.0;
+  }
+  if (!ctx->cfg.keep_arena)
+    for (int i = 0; i < ngpus; ++i) free_arena(ctx->devs[(size_t)i].get());
+  out->healthy = out->failed == 0;
+  out->duration_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return GP_OK;
 }
 

@@ -289,6 +289,11 @@ cudaError_t launch_pattern_verify(const uint64_t* words, uint64_t nwords, int ki
   return cudaGetLastError();
 }
 
+cudaError_t launch_verify_fold(void* scratch, gp_pattern_result* d_result, cudaStream_t stream) {
+  pattern_verify_finalize_kernel<kPatNone><<<1, kThreads, 0, stream>>>(nullptr, 0, reinterpret_cast<VerifySlot*>(scratch), d_result);
+  return cudaGetLastError();
+}
+
 __global__ void bitflip_kernel(uint64_t* words, uint64_t word_index, int bit) {
   words[word_index] ^= (1ull << (bit & 63));
 }

@@ -19,7 +19,7 @@ from typing import List, Optional, Sequence, Tuple
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "libgpuprobe.so")
 
-GP_ABI_VERSION = 1
+GP_ABI_VERSION = 2
 
 GP_PAT_WALKING_ONES, GP_PAT_WALKING_ZEROS, GP_PAT_ADDRESS = 0, 1, 2
 GP_PROBE_COPY, GP_PROBE_TRIAD, GP_PROBE_PATTERN, GP_PROBE_GEMM = 1, 2, 4, 8
@@ -32,6 +32,13 @@ GP_STREAM_AUTO, GP_STREAM_VEC, GP_STREAM_TMA = 0, 1, 2
 GP_OK = 0
 GP_ERR_INVALID, GP_ERR_NO_DEVICE, GP_ERR_CUDA, GP_ERR_NCCL = -1, -2, -3, -4
 GP_ERR_NOMEM, GP_ERR_UNSUPPORTED, GP_ERR_STRUCT_SIZE, GP_ERR_TOO_LARGE = -5, -6, -7, -8
+GP_ERR_DEVICE_LOST = -9
+GP_ARENA_AUTO, GP_ARENA_VMM, GP_ARENA_MALLOC = 0, 1, 2
+GP_GEMM_AUTO, GP_GEMM_1CTA_128x256, GP_GEMM_2CTA_256x256, GP_GEMM_2CTA_256x512 = 0, 1, 2, 3
+GP_TEST_FAULT_GEMM_SKIP_TILE, GP_TEST_FAULT_GEMM_FLIP_BIT = 1, 2
+GP_P2P_READ, GP_P2P_WRITE, GP_P2P_BIDIR_WRITE, GP_P2P_ALL_AT_ONCE = 0, 1, 2, 3
+GP_P2P_BIDIR_READ, GP_P2P_COPY_ENGINE, GP_P2P_COPY_ENGINE_BIDIR = 4, 5, 6
+GP_FABRIC_MAX_GPUS = 16
 
 
 class GpuProbeError(RuntimeError):
@@ -51,6 +58,10 @@ class Config(C.Structure):
         ("seed", C.c_uint64),
         ("min_copy_gbps", C.c_double), ("min_triad_gbps", C.c_double),
         ("min_gemm_tflops", C.c_double), ("gemm_tol", C.c_double),
+        ("min_p2p_gbps", C.c_double), ("max_p2p_spread", C.c_double),
+        ("min_allreduce_busbw_gbps", C.c_double), ("fabric_bytes", C.c_uint64),
+        ("arena_backend", C.c_uint32), ("sm_limit", C.c_uint32),
+        ("gemm_variant", C.c_uint32), ("test_fault", C.c_uint32), ("reserved2", C.c_uint32 * 2),
     ]
 
 
@@ -74,7 +85,7 @@ class GemmResult(C.Structure):
                 ("t", Timing), ("tflops_best", C.c_double), ("tflops_median", C.c_double),
                 ("max_scaled_err", C.c_double), ("freivalds_err", C.c_double),
                 ("samples", C.c_uint32), ("samples_bad", C.c_uint32), ("c_checksum", C.c_uint64),
-                ("output_bf16", C.c_uint32), ("reserved", C.c_uint32)]
+                ("output_bf16", C.c_uint32), ("reserved", C.c_uint32), ("bf16_mismatches", C.c_uint64)]
 
 
 class DeviceResult(C.Structure):
@@ -95,7 +106,29 @@ class DeviceResult(C.Structure):
         ("first_bad_kind", C.c_int32), ("first_bad_pass", C.c_int32),
         ("first_bad_index", C.c_uint64), ("first_bad_xor", C.c_uint64),
         ("pattern_digest", C.c_uint64), ("gemm", GemmResult),
+        ("alloc_s", C.c_double), ("free_s", C.c_double), ("kernels_s", C.c_double),
+        ("arena_bytes", C.c_uint64), ("arena_reused", C.c_uint32), ("arena_backend", C.c_uint32),
     ]
+
+
+class FabricResult(C.Structure):
+    _N2 = GP_FABRIC_MAX_GPUS * GP_FABRIC_MAX_GPUS
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("ngpus", C.c_uint32), ("bytes", C.c_uint64),
+        ("read_gbps", C.c_double * _N2), ("write_gbps", C.c_double * _N2),
+        ("read_min", C.c_double), ("read_max", C.c_double), ("read_mean", C.c_double),
+        ("write_min", C.c_double), ("write_max", C.c_double), ("write_mean", C.c_double),
+        ("spread", C.c_double), ("worst_src", C.c_int32), ("worst_dst", C.c_int32),
+        ("worst_gbps", C.c_double),
+        ("allreduce_algbw_gbps", C.c_double), ("allreduce_busbw_gbps", C.c_double),
+        ("allreduce_error", C.c_int32), ("data_ok", C.c_uint32), ("failed", C.c_uint32),
+        ("healthy", C.c_int32), ("duration_s", C.c_double),
+    ]
+
+    def matrix(self, which: str) -> List[List[float]]:
+        n = self.ngpus
+        m = self.read_gbps if which == "read" else self.write_gbps
+        return [[m[r * n + c] for c in range(n)] for r in range(n)]
 
 
 class NvmlInfo(C.Structure):
@@ -115,6 +148,11 @@ ABI = [
     ("gp_init", C.c_int, [_P(Config), _P(C.c_void_p)]),
     ("gp_shutdown", None, [C.c_void_p]),
     ("gp_trim", C.c_int, [C.c_void_p]),
+    ("gp_trim_device", C.c_int, [C.c_void_p, C.c_char_p]),
+    ("gp_device_reset", C.c_int, [C.c_void_p, C.c_char_p]),
+    ("gp_device_poisoned", C.c_int, [C.c_void_p, C.c_char_p]),
+    ("gp_inject_cuda_error", C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
+    ("gp_probe_fabric", C.c_int, [C.c_void_p, C.c_int, _P(FabricResult)]),
     ("gp_abi_version", C.c_uint32, []),
     ("gp_sizeof", C.c_size_t, [C.c_int]),
     ("gp_strerror", C.c_char_p, [C.c_int]),
@@ -233,6 +271,22 @@ class Probe:
     def trim(self) -> None:
         self._check(self.lib.gp_trim(self._ctx), "gp_trim")
 
+    def trim_device(self, uuid) -> None:
+        self._check(self.lib.gp_trim_device(self._ctx, _u(uuid)), "gp_trim_device")
+
+    def device_reset(self, uuid) -> None:
+        self._check(self.lib.gp_device_reset(self._ctx, _u(uuid)), "gp_device_reset")
+
+    def device_poisoned(self, uuid) -> bool:
+        rc = self.lib.gp_device_poisoned(self._ctx, _u(uuid))
+        if rc < 0:
+            self._check(rc, "gp_device_poisoned")
+        return bool(rc)
+
+    def inject_cuda_error(self, uuid, cuda_error: int) -> int:
+        """Test-only: returns the gp_error the failing call would have returned (no exception)."""
+        return self.lib.gp_inject_cuda_error(self._ctx, _u(uuid), cuda_error)
+
     def nvml_snapshot(self, uuid) -> NvmlInfo:
         out = NvmlInfo()
         self._check(self.lib.gp_nvml_snapshot(self._ctx, _u(uuid), C.byref(out)), "gp_nvml_snapshot")
@@ -310,6 +364,11 @@ class Probe:
         arr = (C.c_double * (ngpus * ngpus))()
         self._check(self.lib.gp_probe_p2p(self._ctx, ngpus, nbytes, direction, arr), "gp_probe_p2p")
         return [[arr[r * ngpus + c] for c in range(ngpus)] for r in range(ngpus)]
+
+    def probe_fabric(self, ngpus: int) -> FabricResult:
+        out = FabricResult()
+        self._check(self.lib.gp_probe_fabric(self._ctx, ngpus, C.byref(out)), "gp_probe_fabric")
+        return out
 
     def probe_allreduce(self, nranks: int, nbytes: int, warmup: int = 2, iters: int = 10) -> Tuple[float, float]:
         alg, bus = C.c_double(), C.c_double()

@@ -26,6 +26,12 @@ struct ProbeConfig {
   std::string GemmOutput = "fp32";  // "fp32" (strictest check) or "bf16" (what cuBLAS bf16 peaks write)
   double MinCopyGbps = 0, MinTriadGbps = 0, MinGemmTflops = 0;  // 0 = floor not enforced
   int IntervalSeconds = 0;                                       // 0 = no periodic re-probe
+  // fabric (K4): measured once per loadPlugins when every full GPU is idle; floors 0 = not enforced
+  bool Fabric = true;
+  double MinP2PGbps = 0, MaxP2PSpread = 0, MinAllreduceBusbwGbps = 0;
+  uint64_t FabricBytes = 0;          // 0 = 1 GiB per transfer
+  bool KeepArena = false;            // keep the arena of an idle device mapped between re-probes (freed in Allocate)
+  bool Isolate = false;              // every periodic re-probe of a full GPU from a child process
 };
 struct Config {
   std::string WebListenAddress = "9002";  // config.go:17 (no colon — the reference's own default)
@@ -46,6 +52,11 @@ struct Config {
     c.min_copy_gbps = Probe.MinCopyGbps;
     c.min_triad_gbps = Probe.MinTriadGbps;
     c.min_gemm_tflops = Probe.MinGemmTflops;
+    c.min_p2p_gbps = Probe.MinP2PGbps;
+    c.max_p2p_spread = Probe.MaxP2PSpread;
+    c.min_allreduce_busbw_gbps = Probe.MinAllreduceBusbwGbps;
+    c.fabric_bytes = Probe.FabricBytes;
+    c.keep_arena = Probe.KeepArena ? 1u : 0u;
     return c;
   }
 };
@@ -104,6 +115,13 @@ inline Config LoadConfig(const std::string& yamlText) {
   if (auto v = get("probe.minTriadGbps")) c.Probe.MinTriadGbps = std::stod(*v);
   if (auto v = get("probe.minGemmTflops")) c.Probe.MinGemmTflops = std::stod(*v);
   if (auto v = get("probe.intervalSeconds")) c.Probe.IntervalSeconds = std::stoi(*v);
+  if (auto v = get("probe.fabric")) c.Probe.Fabric = truthy(*v);
+  if (auto v = get("probe.minP2PGbps")) c.Probe.MinP2PGbps = std::stod(*v);
+  if (auto v = get("probe.maxP2PSpread")) c.Probe.MaxP2PSpread = std::stod(*v);
+  if (auto v = get("probe.minAllreduceBusbwGbps")) c.Probe.MinAllreduceBusbwGbps = std::stod(*v);
+  if (auto v = get("probe.fabricBytes")) c.Probe.FabricBytes = std::stoull(*v);
+  if (auto v = get("probe.keepArena")) c.Probe.KeepArena = truthy(*v);
+  if (auto v = get("probe.isolate")) c.Probe.Isolate = truthy(*v);
   return c;
 }
 

@@ -29,7 +29,7 @@ struct FakeInfo : deviceInfo {
 struct FakeBackend : ProbeBackend {
   std::set<std::string> bad, err, busy;
   int many_calls = 0, slice_calls = 0;
-  int OtherComputeProcs(const std::string& u) override { return busy.count(u) ? 2 : 0; }
+  int OtherComputeProcs(const std::string& u) override { return unknown_busy ? -1 : (busy.count(u) ? 2 : 0); }
   static gp_device_result mk(const std::string& u, bool healthy) {
     gp_device_result r{};
     r.struct_size = sizeof(r);
@@ -45,10 +45,41 @@ struct FakeBackend : ProbeBackend {
     int rc = 0;
     for (auto& u : uuids) {
       out->push_back(mk(u, !bad.count(u)));
+      if (nomem.count(u)) { out->back().error = GP_ERR_NOMEM; out->back().healthy = 0; rc = GP_ERR_NOMEM; }
       if (err.count(u)) { out->back().error = GP_ERR_CUDA; out->back().healthy = 0; rc = GP_ERR_CUDA; if (e) *e = u + ": xid"; }
     }
     return rc;
   }
+  // fabric script: flat 780 GB/s except the pairs in `slow_pairs`
+  std::vector<std::pair<int, int>> slow_pairs;
+  std::vector<std::string> fabric_uuids;
+  int fabric_calls = 0, isolated_calls = 0, resets = 0;
+  std::vector<std::string> trimmed;
+  int unknown_busy = 0;  // OtherComputeProcs answers -1 for everything
+  std::set<std::string> nomem;
+  int ProbeFabric(int n, gp_fabric_result* out, std::vector<std::string>* uuids, std::string*) override {
+    ++fabric_calls;
+    gp_fabric_result f{};
+    f.struct_size = sizeof(f); f.ngpus = (uint32_t)n; f.bytes = 1ull << 30; f.data_ok = 1; f.healthy = 1; f.spread = 1.0;
+    f.worst_src = f.worst_dst = -1; f.worst_gbps = 780;
+    for (int i = 0; i < n * n; ++i) { f.read_gbps[i] = 780; f.write_gbps[i] = 713; }
+    for (auto pr : slow_pairs) {
+      f.read_gbps[pr.first * n + pr.second] = f.read_gbps[pr.second * n + pr.first] = 90;
+      f.write_gbps[pr.first * n + pr.second] = f.write_gbps[pr.second * n + pr.first] = 85;
+      f.worst_src = pr.first; f.worst_dst = pr.second; f.worst_gbps = 85; f.spread = 780.0 / 85; f.failed = 1 | 2; f.healthy = 0;
+    }
+    f.allreduce_busbw_gbps = 830;
+    *out = f;
+    if (uuids) *uuids = fabric_uuids;
+    return 0;
+  }
+  int ProbeIsolated(const std::string& u, uint32_t, uint64_t, gp_device_result* out, std::string*) override {
+    ++isolated_calls;
+    *out = mk(u, !bad.count(u));
+    return 0;
+  }
+  void TrimDevice(const std::string& u) override { trimmed.push_back(u); }
+  int ResetDevice(const std::string&) override { ++resets; return 0; }
   uint64_t last_slice_mem = 0;
   int ProbeSlice(const std::string& u, uint32_t, uint64_t total_mem, gp_device_result* out, std::string*) override {
     ++slice_calls;
@@ -208,6 +239,93 @@ int main() {
     PluginManager bad(MigStrategyNone, {Resource::New("GPU", "gpu")}, [&] { return nodes; }, &fb, &pm, 1);
     CHECK(bad.loadPlugins().value() == "GPU name 'NVIDIA B200' does not match any resource patterns");
   }
+  // --- loadPlugins / restartPlugins never give the full probe to a device tenants are using ---
+  {
+    FakeBackend fb;
+    ProbeMetrics pm;
+    PluginManager mgr(MigStrategySingle, {Resource::New("*", "gpu")}, [&] { return nodes; }, &fb, &pm, GP_PROBE_ALL_SINGLE);
+    mgr.EnableFabric(false);
+    fb.bad = {"GPU-n1"};
+    CHECK(!mgr.loadPlugins() && mgr.unhealthyAtLoad() == 1);      // idle node: both graded, n1 fails
+    fb.bad.clear();
+    fb.busy = {"GPU-n0", "GPU-n1"};                                 // pods arrive; kubelet restarts -> restartPlugins
+    const int calls = fb.many_calls;
+    CHECK(!mgr.restartPlugins() && fb.many_calls == calls);         // nobody was probed
+    auto& g = mgr.devices().m["nvidia.com/gpu"];
+    CHECK(g.GetByID("GPU-n0")->Health == std::string(Healthy));    // kept: last verdict healthy
+    CHECK(g.GetByID("GPU-n1")->Health == std::string(Unhealthy));  // kept: last verdict unhealthy, not silently healed
+    CHECK(mgr.skippedBusy() == 2 && mgr.unhealthyAtLoad() == 0);
+    FakeBackend small;
+    mgr.SetReducedBackend(&small, GP_PROBE_COPY | GP_PROBE_PATTERN);
+    CHECK(!mgr.restartPlugins() && small.many_calls == 1 && fb.many_calls == calls && mgr.reducedProbes() == 2);
+    // NVML missing: busy-ness unknown.  The full probe is tried; out of memory then means "in use", not "broken"
+    FakeBackend blind;
+    blind.unknown_busy = 1;
+    blind.nomem = {"GPU-n0"};
+    PluginManager m2(MigStrategySingle, {Resource::New("*", "gpu")}, [&] { return nodes; }, &blind, &pm, GP_PROBE_ALL_SINGLE);
+    m2.EnableFabric(false);
+    CHECK(!m2.loadPlugins() && m2.unhealthyAtLoad() == 0 && m2.notGraded() == 1);
+    CHECK(m2.devices().m["nvidia.com/gpu"].GetByID("GPU-n0")->Health == std::string(Healthy));
+    blind.unknown_busy = 0;                                         // with NVML answering "idle", NOMEM is a real failure
+    PluginManager m3(MigStrategySingle, {Resource::New("*", "gpu")}, [&] { return nodes; }, &blind, &pm, GP_PROBE_ALL_SINGLE);
+    m3.EnableFabric(false);
+    CHECK(!m3.loadPlugins() && m3.unhealthyAtLoad() == 1);
+  }
+  // --- fabric: measured once per load, feeds the gauges and the allocator, steers around a degraded pair ---
+  {
+    std::vector<GpuNode> four;
+    for (int i = 0; i < 4; ++i) four.push_back({i, "NVIDIA B200", false, mkinfo("GPU-f" + std::to_string(i)), {}});
+    FakeBackend fb;
+    fb.fabric_uuids = {"GPU-f0", "GPU-f1", "GPU-f2", "GPU-f3"};
+    fb.slow_pairs = {{0, 1}};
+    ProbeMetrics pm;
+    PluginManager mgr(MigStrategyNone, {Resource::New("*", "gpu")}, [&] { return four; }, &fb, &pm, GP_PROBE_ALL_SINGLE);
+    CHECK(!mgr.loadPlugins() && fb.fabric_calls == 1 && mgr.fabric().healthy == 0 && mgr.fabric().worst_src == 0);
+    const std::string text = pm.Render();
+    CHECK(text.find("gpu_probe_p2p_gbps{dir=\"read\",dst=\"1\",src=\"0\"} 90") != std::string::npos);
+    CHECK(text.find("gpu_probe_p2p_gbps{dir=\"write\",dst=\"3\",src=\"2\"} 713") != std::string::npos);
+    CHECK(text.find("gpu_probe_allreduce_busbw_gbps{ranks=\"4\"} 830") != std::string::npos);
+    CHECK(text.find("gpu_probe_fabric_healthy{gpus=\"4\"} 0") != std::string::npos);
+    bool logged = false;
+    for (auto& l : mgr.log()) logged = logged || l.find("fabric graded unhealthy") != std::string::npos;
+    CHECK(logged);
+    auto [pick, pe] = mgr.PreferredAllocation("nvidia.com/gpu", fb.fabric_uuids, {"GPU-f0"}, 3);
+    CHECK(!pe && pick.size() == 3 && pick[0] == "GPU-f0" && std::find(pick.begin(), pick.end(), "GPU-f1") == pick.end());
+    auto [pick2, pe2] = mgr.PreferredAllocation("nvidia.com/gpu", fb.fabric_uuids, {}, 2);
+    CHECK(!pe2 && !(std::count(pick2.begin(), pick2.end(), "GPU-f0") && std::count(pick2.begin(), pick2.end(), "GPU-f1")));
+    CHECK(mgr.PreferredAllocation("nvidia.com/nope", {}, {}, 1).second.has_value());
+    // busy GPUs: the fabric probe (it drives every GPU at once) is not run
+    fb.busy = {"GPU-f2"};
+    CHECK(!mgr.restartPlugins() && fb.fabric_calls == 1);
+    // Allocate hands the kept probe arena back before the pod starts
+    auto [env2, ae4] = mgr.plugins()[0]->Allocate({"GPU-f1", "GPU-f3"});
+    CHECK(!ae4 && env2 == "NVIDIA_VISIBLE_DEVICES=GPU-f1,GPU-f3" && fb.trimmed == std::vector<std::string>({"GPU-f1", "GPU-f3"}));
+  }
+  // --- a context lost to a sticky fault: re-graded from a child process, then reset in-process ---
+  {
+    FakeBackend fb;
+    ProbeMetrics pm;
+    PluginManager mgr(MigStrategySingle, {Resource::New("*", "gpu")}, [&] { return nodes; }, &fb, &pm, GP_PROBE_ALL_SINGLE);
+    mgr.EnableFabric(false);
+    CHECK(!mgr.loadPlugins());
+    auto plug0 = mgr.plugins()[0];
+    std::vector<std::vector<PluginDevice>> got;
+    std::thread t([&] { plug0->ListAndWatch([&](const std::vector<PluginDevice>& l) { got.push_back(l); return true; }); });
+    auto lost = std::make_shared<gp_device_result>(FakeBackend::mk("GPU-n0", false));
+    lost->error = GP_ERR_DEVICE_LOST;
+    mgr.devices().m["nvidia.com/gpu"].GetByID("GPU-n0")->Probe = lost;   // what an Xid during a probe leaves behind
+    plug0->Report("GPU-n0", false);
+    const int many = fb.many_calls;
+    auto [gr, ge] = mgr.Reprobe();
+    CHECK(!ge && gr.size() == 2 && fb.isolated_calls == 1 && fb.resets == 1 && fb.many_calls == many + 1);  // n1 in-process, n0 isolated
+    CHECK(mgr.isolatedProbes() == 1 && VerdictHealthy(*mgr.devices().m["nvidia.com/gpu"].GetByID("GPU-n0")));
+    mgr.SetIsolation(true);                                            // policy: every periodic re-probe isolated
+    mgr.Reprobe();
+    CHECK(fb.isolated_calls == 3 && fb.many_calls == many + 1 && fb.resets == 1);
+    plug0->Stop();
+    t.join();
+    CHECK(got.size() == 3 && health_of(got[1], "GPU-n0") == "Unhealthy" && health_of(got[2], "GPU-n0") == "Healthy");
+  }
   // --- preferred allocation ---
   {
     Devices reps;
@@ -251,6 +369,10 @@ int main() {
     CHECK(g.struct_size == sizeof(gp_config) && g.hbm_bytes == (1ull << 30) && g.min_copy_gbps == 6000 && g.gemm_output == 0);
     CHECK(LoadConfig("probe:\n  gemmOutput: bf16\n").ToGpConfig().gemm_output == 1);
     CHECK(LoadConfig("probe:\n  patternBytes: all\n").ToGpConfig().pattern_bytes == GP_PATTERN_ALL_FREE);
+    Config f3 = LoadConfig("probe:\n  minP2PGbps: 600\n  maxP2PSpread: 1.2\n  minAllreduceBusbwGbps: 500\n  fabricBytes: 268435456\n  keepArena: true\n  isolate: true\n  fabric: false\n");
+    gp_config fg = f3.ToGpConfig();
+    CHECK(fg.min_p2p_gbps == 600 && fg.max_p2p_spread == 1.2 && fg.min_allreduce_busbw_gbps == 500 && fg.fabric_bytes == (256ull << 20) && fg.keep_arena == 1);
+    CHECK(f3.Probe.Isolate && !f3.Probe.Fabric && LoadConfig("").Probe.Fabric && LoadConfig("").ToGpConfig().keep_arena == 0);
   }
   printf("host_selftest ok\n");
   return 0;

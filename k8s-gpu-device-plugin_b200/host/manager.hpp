@@ -203,19 +203,61 @@ class PluginManager {
         be_(be), metrics_(metrics), mask_(mask) {}
   ~PluginManager() { StopTicker(); }
 
-  // manager.go:156-174, plus the grade: kubelet never sees an ungraded device
+  // manager.go:156-174, plus the grade: kubelet never sees an ungraded device.
+  //
+  // restartPlugins runs this again on every kubelet socket re-creation and every GET /restart
+  // (manager.go:177-194), i.e. on nodes whose GPUs are running pods.  A device somebody else is
+  // computing on is therefore never given the full probe here (3 x 16 GiB and every SM would either
+  // fail to allocate or trample the tenant): it gets the reduced probe when a reduced backend is set,
+  // else it keeps the verdict of its last grade (Healthy if it never had one).  When busy-ness cannot
+  // be told (no NVML) the full probe is tried, but running out of memory then means "in use, not
+  // graded", not "unhealthy".
   Error loadPlugins() {
     auto [dm, err] = NewDeviceMap(enumerate_(), resources_, migStrategy_);
     if (err) return err;
     std::lock_guard<std::mutex> g(mu_);
     devices_ = std::move(dm);
-    unhealthy_at_load_ = GradeDevices(devices_, *be_, mask_, &log_);
-    for (auto& d : devices_.All()) metrics_->Update(*d);
+    DeviceMap idle, busy;
+    std::map<std::string, int> procs;
+    int n_busy = 0;
+    for (auto& kv : devices_.m)
+      for (auto& dv : kv.second.m) {
+        const std::string u = dv.second->GetUUID();
+        if (!procs.count(u)) procs[u] = be_->OtherComputeProcs(u);
+        if (procs[u] > 0) { busy.m[kv.first].m[dv.first] = dv.second; ++n_busy; }
+        else idle.m[kv.first].m[dv.first] = dv.second;
+      }
+    unhealthy_at_load_ = 0;
+    if (!idle.m.empty()) unhealthy_at_load_ += GradeDevices(idle, *be_, mask_, &log_);
+    for (auto& d : idle.All())  // unknown busy-ness + out of memory = a tenant holds the memory: not graded
+      if (procs[d->GetUUID()] < 0 && d->Probe && d->Probe->error == GP_ERR_NOMEM) { KeepLastVerdict(*d); --unhealthy_at_load_; ++not_graded_; }
+    if (!busy.m.empty()) {
+      if (reduced_be_) { unhealthy_at_load_ += GradeDevices(busy, *reduced_be_, reduced_mask_, &log_); reduced_probes_ += n_busy; }
+      else for (auto& d : busy.All()) { KeepLastVerdict(*d); ++skipped_busy_; }
+    }
+    for (auto& d : devices_.All()) { metrics_->Update(*d); if (d->Probe) last_[d->GetUUID()] = d->Probe; }
+    // the fabric is graded once per load, with every full GPU idle and healthy (it drives all of them at once)
+    if (fabric_enabled_ && n_busy == 0) GradeFabric();
     plugins_.clear();
-    for (auto& kv : devices_.m) plugins_.push_back(std::make_shared<NvidiaDevicePlugin>(kv.first, kv.second));
+    for (auto& kv : devices_.m) {
+      auto pl = std::make_shared<NvidiaDevicePlugin>(kv.first, kv.second);
+      pl->SetOnAllocate([this](const std::vector<std::string>& ids) { for (auto& id : ids) be_->TrimDevice(AnnotatedID{id}.GetID()); });
+      plugins_.push_back(pl);
+    }
     ++loads_;
     return std::nullopt;
   }
+  // plugin/plugin.go:192-207 GetPreferredAllocation for resource `name`, ranking by the measured matrix
+  std::pair<std::vector<std::string>, Error> PreferredAllocation(const std::string& name, const std::vector<std::string>& available,
+                                                                 const std::vector<std::string>& mustInclude, int size) {
+    std::lock_guard<std::mutex> g(mu_);
+    auto it = devices_.m.find(name);
+    if (it == devices_.m.end()) return {{}, "unknown resource " + name};
+    return getPreferredAllocation(it->second, fabric_matrix_, available, mustInclude, size);
+  }
+  void EnableFabric(bool on) { fabric_enabled_ = on; }
+  const gp_fabric_result& fabric() const { return fabric_; }
+  const P2PMatrix& fabricMatrix() const { return fabric_matrix_; }
   // manager.go:108-110 sets a flag that the Start loop polls (manager.go:93-97); here the poll is explicit
   void Restart() { restart_ = true; }
   Error poll() {
@@ -241,7 +283,7 @@ class PluginManager {
       for (auto& dv : kv.second.m)
         if (uuid.empty() || dv.second->GetUUID() == uuid) {
           known = true;
-          if (skip_busy && be_->OtherComputeProcs(dv.second->GetUUID()) > 0) {
+          if (skip_busy && be_->OtherComputeProcs(dv.second->GetUUID()) > 0) {  // -1 (unknown) counts as idle here: the arena request then decides
             if (reduced_be_) { busy.m[kv.first].m[dv.first] = dv.second; ++reduced_probes_; }
             else ++skipped_busy_;
             continue;
@@ -250,17 +292,35 @@ class PluginManager {
         }
     if (!known) return {{}, "unknown device " + uuid};
     if (scope.m.empty() && busy.m.empty()) return {{}, std::nullopt};
-    if (!scope.m.empty()) GradeDevices(scope, *be_, mask_, &log_, /*apply_health=*/false);
+    // a device whose in-process context was lost to a sticky fault (or every device, with isolation on) is
+    // graded from a fresh child process: the fault cannot reach this process, and a lost context cannot
+    // keep a repaired GPU Unhealthy for ever.  If the child finds the GPU healthy, the in-process context
+    // is reset so the fast path works again.
+    DeviceMap inproc, isolated;
+    for (auto& kv : scope.m)
+      for (auto& dv : kv.second.m) {
+        const bool lost = dv.second->Probe && dv.second->Probe->error == GP_ERR_DEVICE_LOST;
+        if (!dv.second->IsMigDevice() && (isolate_ || lost)) isolated.m[kv.first].m[dv.first] = dv.second;
+        else inproc.m[kv.first].m[dv.first] = dv.second;
+      }
+    if (!inproc.m.empty()) GradeDevices(inproc, *be_, mask_, &log_, /*apply_health=*/false);
+    if (!isolated.m.empty()) GradeIsolated(isolated);
     if (!busy.m.empty()) GradeDevices(busy, *reduced_be_, reduced_mask_, &log_, /*apply_health=*/false);
     auto all = scope.All();
     for (auto& d : busy.All()) all.push_back(d);
     for (auto& d : all) {
       metrics_->Update(*d);
+      if (d->Probe) last_[d->GetUUID()] = d->Probe;
       for (auto& p : plugins_) if (p->devices().GetByID(d->ID)) p->Report(d->ID, VerdictHealthy(*d));
     }
     ++reprobes_;
     return {all, std::nullopt};
   }
+  // every full-GPU re-probe through a child process (slower: context creation and a cold arena per call)
+  void SetIsolation(bool on) { isolate_ = on; }
+  int isolatedProbes() const { return isolated_probes_; }
+  int notGraded() const { return not_graded_; }
+
   void StartTicker(std::chrono::milliseconds interval) {
     StopTicker();
     ticking_ = true;
@@ -289,6 +349,66 @@ class PluginManager {
   std::vector<std::string> log() { std::lock_guard<std::mutex> g(mu_); return log_; }
 
  private:
+  // not graded this time: the device keeps the verdict of its last grade (Healthy if it never had one)
+  void KeepLastVerdict(Device& d) {
+    auto it = last_.find(d.GetUUID());
+    if (it != last_.end()) { d.Probe = it->second; d.Health = VerdictHealthy(d) ? Healthy : Unhealthy; }
+    else { d.Probe = nullptr; d.Health = Healthy; }
+  }
+  void GradeIsolated(DeviceMap& dm) {
+    auto devs = dm.All();
+    std::vector<gp_device_result> res(devs.size());
+    std::vector<int> rcs(devs.size(), 0);
+    std::vector<std::string> errs(devs.size());
+    std::vector<std::thread> th;
+    for (size_t i = 0; i < devs.size(); ++i)
+      th.emplace_back([&, i] { rcs[i] = be_->ProbeIsolated(devs[i]->GetUUID(), mask_, devs[i]->TotalMemory, &res[i], &errs[i]); });
+    for (auto& t : th) t.join();
+    for (size_t i = 0; i < devs.size(); ++i) {
+      ++isolated_probes_;
+      const bool ok = rcs[i] == GP_OK && res[i].error == 0 && res[i].healthy == 1;
+      auto pr = std::make_shared<gp_device_result>(res[i]);
+      if (!ok) { pr->healthy = 0; if (pr->error == 0) pr->error = rcs[i] ? rcs[i] : GP_ERR_CUDA; }
+      const bool was_lost = devs[i]->Probe && devs[i]->Probe->error == GP_ERR_DEVICE_LOST;
+      devs[i]->Probe = pr;
+      if (!ok) log_.push_back("'" + devs[i]->ID + "' graded unhealthy from a child process: rc=" + std::to_string(rcs[i]) + (errs[i].empty() ? "" : " (" + errs[i] + ")"));
+      else if (was_lost) {
+        const int rr = be_->ResetDevice(devs[i]->GetUUID());
+        log_.push_back("'" + devs[i]->ID + "' healthy again from a fresh process; in-process context reset rc=" + std::to_string(rr));
+      }
+    }
+  }
+  // K4 once per load: matrix for the allocator, gauges, verdict in the log
+  void GradeFabric() {
+    std::vector<std::string> full;
+    for (auto& d : devices_.All())
+      if (!d->IsMigDevice() && !AnnotatedID{d->ID}.HasAnnotations()) full.push_back(d->GetUUID());
+    std::sort(full.begin(), full.end());
+    full.erase(std::unique(full.begin(), full.end()), full.end());
+    if (full.size() < 2 || full.size() > GP_FABRIC_MAX_GPUS) return;
+    std::vector<std::string> uuids;
+    std::string err;
+    gp_fabric_result f{};
+    const int rc = be_->ProbeFabric((int)full.size(), &f, &uuids, &err);
+    if (rc != GP_OK) { log_.push_back("fabric probe failed: rc=" + std::to_string(rc) + (err.empty() ? "" : " (" + err + ")")); return; }
+    fabric_ = f;
+    const int n = (int)f.ngpus;
+    fabric_matrix_.uuidByOrdinal = uuids;
+    fabric_matrix_.gbps.assign((size_t)n * n, 0.0);
+    for (int i = 0; i < n; ++i)
+      for (int j = 0; j < n; ++j) {
+        // what a pair can sustain in the slower of its two modes; the allocator takes min(i->j, j->i) of this
+        fabric_matrix_.gbps[(size_t)(i * n + j)] = std::min(f.read_gbps[i * n + j], f.write_gbps[i * n + j]);
+        if (i != j) { metrics_->SetP2P(i, j, "read", f.read_gbps[i * n + j]); metrics_->SetP2P(i, j, "write", f.write_gbps[i * n + j]); }
+      }
+    if (f.allreduce_error == 0) metrics_->SetAllReduce(n, f.allreduce_busbw_gbps);
+    metrics_->Set("gpu_probe_fabric_healthy", "1 if the P2P matrix and the all-reduce met their floors and every transfer carried the right bytes", "gpus=\"" + std::to_string(n) + "\"", f.healthy);
+    metrics_->Set("gpu_probe_fabric_spread", "max/min over the off-diagonal P2P pairs (1.0 = flat)", "gpus=\"" + std::to_string(n) + "\"", f.spread);
+    if (!f.healthy)
+      log_.push_back("fabric graded unhealthy: failed=" + std::to_string(f.failed) + " worst pair " + std::to_string(f.worst_src) + "->" +
+                     std::to_string(f.worst_dst) + " at " + std::to_string(f.worst_gbps) + " GB/s, spread " + std::to_string(f.spread));
+  }
+
   std::string migStrategy_;
   std::vector<Resource> resources_;
   Enumerate enumerate_;
@@ -304,6 +424,11 @@ class PluginManager {
   ProbeBackend* reduced_be_ = nullptr;
   uint32_t reduced_mask_ = GP_PROBE_COPY | GP_PROBE_PATTERN;
   int unhealthy_at_load_ = 0;
+  std::map<std::string, std::shared_ptr<gp_device_result>> last_;  // by uuid, survives restartPlugins
+  bool fabric_enabled_ = true, isolate_ = false;
+  gp_fabric_result fabric_{};
+  P2PMatrix fabric_matrix_;
+  std::atomic<int> isolated_probes_{0}, not_graded_{0};
   std::thread ticker_;
   std::mutex tick_mu_;
   std::condition_variable tick_cv_;

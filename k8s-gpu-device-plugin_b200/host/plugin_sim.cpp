@@ -4,11 +4,13 @@
 // There is no kubelet, gRPC or HTTP server here (out of scope); the handlers are called
 // directly.  Used by tests/test_host_gpu.py.
 //   plugin_sim [--hbm-mib N] [--pattern-mib N] [--wo N] [--gemm N] [--mask M] [--slice BIN] [--min-copy G]
+//              [--scenario manager] [--fabric-mib N] [--min-p2p G]
 #include <cstdio>
 #include <cstring>
 #include <string>
 #include <thread>
 
+#include "manager.hpp"
 #include "router.hpp"
 
 using namespace plugin;
@@ -35,6 +37,82 @@ static std::string listJson(const std::vector<PluginDevice>& l) {
   return s + "]";
 }
 
+// --scenario manager: the PluginManager path on real GPUs — loadPlugins grades every GPU and then the fabric
+// (P2P matrix + all-reduce) in one go, the matrix feeds the gauges and GetPreferredAllocation; then the
+// isolation path: a child that faults, a child that never answers (killed at the deadline), and the way back.
+static int manager_scenario(gp_config cfg, uint32_t mask, const std::string& slice_bin) {
+  cfg.keep_arena = 1;
+  GpuProbeBackend be(&cfg, slice_bin);
+  if (be.init_rc()) { printf("{\"error\":\"gp_init: %s\"}\n", be.init_error().c_str()); return 1; }
+  const int n = gp_device_count(be.ctx());
+  std::vector<std::shared_ptr<CudaDeviceInfo>> infos;
+  for (int i = 0; i < n; ++i) {
+    auto info = std::make_shared<CudaDeviceInfo>();
+    char uuid[64];
+    gp_device_uuid(be.ctx(), i, uuid, sizeof(uuid));
+    gp_probe_device(be.ctx(), uuid, 0, &info->id);
+    infos.push_back(info);
+  }
+  auto enumerate = [&] {
+    std::vector<GpuNode> nodes;
+    for (int i = 0; i < n; ++i) nodes.push_back({i, "NVIDIA B200", false, infos[(size_t)i], {}});
+    return nodes;
+  };
+  ProbeMetrics metrics;
+  PluginManager mgr(MigStrategyNone, {Resource::New("*", "gpu")}, enumerate, &be, &metrics, mask);
+  if (auto e = mgr.loadPlugins()) { printf("{\"error\":\"%s\"}\n", jsonEscape(*e).c_str()); return 1; }
+  const gp_fabric_result& f = mgr.fabric();
+  std::vector<std::string> all_ids = mgr.devices().m["nvidia.com/gpu"].GetIDs();
+  std::string pref = "[";
+  if (n >= 2) {
+    auto [pick, pe] = mgr.PreferredAllocation("nvidia.com/gpu", all_ids, {}, std::min(n, 2));
+    for (size_t i = 0; i < pick.size(); ++i) pref += std::string(i ? "," : "") + "\"" + pick[i] + "\"";
+  }
+  pref += "]";
+  auto plug = mgr.plugins()[0];
+  std::vector<std::string> lists;
+  std::thread law([&] { plug->ListAndWatch([&](const std::vector<PluginDevice>& l) { lists.push_back(listJson(l)); return true; }); });
+  auto health0 = [&] { return std::string(VerdictHealthy(*mgr.devices().m["nvidia.com/gpu"].GetByID(all_ids[0])) ? "Healthy" : "Unhealthy"); };
+  std::string steps = "[";
+  auto step = [&](const char* name) {
+    auto [graded, err] = mgr.Reprobe(all_ids[0]);
+    const Device& d = *mgr.devices().m["nvidia.com/gpu"].GetByID(all_ids[0]);
+    steps += std::string(steps.size() > 1 ? "," : "") + "{\"step\":\"" + name + "\",\"verdict\":\"" + health0() + "\",\"error\":" +
+             std::to_string(d.Probe ? d.Probe->error : 0) + ",\"graded\":" + std::to_string(graded.size()) + "}";
+  };
+  int rc = 0;
+  if (!slice_bin.empty()) {
+    mgr.SetIsolation(true);
+    step("isolated");                                      // fresh child, healthy
+    be.SetChildExtraArgs({"--test-cuda-error", "700"});    // the child's device reports a sticky fault
+    step("child_fault");
+    be.SetChildExtraArgs({});
+    step("after_fault");                                   // next child: healthy again, parent untouched
+    be.SetChildExtraArgs({"--test-hang"});                 // a child that never answers
+    be.SetChildTimeout(std::chrono::milliseconds(1500));
+    step("child_hang");
+    be.SetChildExtraArgs({});
+    be.SetChildTimeout(std::chrono::milliseconds(120000));
+    step("after_hang");
+    mgr.SetIsolation(false);
+    step("in_process");                                    // and the plugin's own context still works
+  }
+  plug->Stop();
+  law.join();
+  steps += "]";
+  printf("{\"devices\":%d,\"unhealthy\":%d,\"fabric\":{\"ngpus\":%u,\"healthy\":%d,\"data_ok\":%u,\"failed\":%u,\"spread\":%.6f,"
+         "\"read_min\":%.1f,\"read_max\":%.1f,\"write_min\":%.1f,\"write_max\":%.1f,\"worst\":[%d,%d],\"allreduce_busbw\":%.1f,"
+         "\"allreduce_error\":%d,\"seconds\":%.3f},\"preferred\":%s,\"steps\":%s,\"isolated_probes\":%d,\"lists\":[",
+         n, mgr.unhealthyAtLoad(), f.ngpus, f.healthy, f.data_ok, f.failed, f.spread, f.read_min, f.read_max, f.write_min, f.write_max,
+         f.worst_src, f.worst_dst, f.allreduce_busbw_gbps, f.allreduce_error, f.duration_s, pref.c_str(), steps.c_str(), mgr.isolatedProbes());
+  for (size_t i = 0; i < lists.size(); ++i) printf("%s%s", i ? "," : "", lists[i].c_str());
+  printf("],\"log\":[");
+  auto log = mgr.log();
+  for (size_t i = 0; i < log.size(); ++i) printf("%s\"%s\"", i ? "," : "", jsonEscape(log[i]).c_str());
+  printf("],\"metrics\":\"%s\"}\n", jsonEscape(metrics.Render()).c_str());
+  return rc;
+}
+
 int main(int argc, char** argv) {
   gp_config cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -47,7 +125,7 @@ int main(int argc, char** argv) {
   cfg.iters = 3;
   cfg.warmup = 1;
   uint32_t mask = GP_PROBE_ALL_SINGLE;
-  std::string slice_bin;
+  std::string slice_bin, scenario;
   for (int i = 1; i + 1 < argc; i += 2) {
     const std::string a = argv[i];
     const char* v = argv[i + 1];
@@ -58,7 +136,11 @@ int main(int argc, char** argv) {
     else if (a == "--mask") mask = (uint32_t)atoi(v);
     else if (a == "--slice") slice_bin = v;
     else if (a == "--min-copy") cfg.min_copy_gbps = atof(v);
+    else if (a == "--scenario") scenario = v;
+    else if (a == "--fabric-mib") cfg.fabric_bytes = strtoull(v, nullptr, 10) << 20;
+    else if (a == "--min-p2p") cfg.min_p2p_gbps = atof(v);
   }
+  if (scenario == "manager") return manager_scenario(cfg, mask, slice_bin);
   GpuProbeBackend be(&cfg, slice_bin);
   if (be.init_rc()) {
     printf("{\"error\":\"gp_init: %s\"}\n", be.init_error().c_str());

@@ -7,6 +7,10 @@
 //   plugin/manager.go:156-174            loadPlugins: grade before startPlugins
 //   plugin/plugin.go:40,53,173-189       `health` channel and ListAndWatch (no writer today)
 #pragma once
+#include <fcntl.h>
+#include <poll.h>
+#include <signal.h>
+#include <spawn.h>
 #include <sys/types.h>
 #include <sys/wait.h>
 #include <unistd.h>
@@ -17,12 +21,15 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
+#include <cerrno>
 #include <cstring>
 #include <deque>
 #include <functional>
 #include <thread>
 
 #include "device.hpp"
+
+extern char** environ;
 
 namespace plugin {
 
@@ -37,9 +44,21 @@ struct ProbeBackend {
   // total_mem is the slice's memory (device/device.go:175-181): the probe is sized to it
   virtual int ProbeSlice(const std::string& mig_uuid, uint32_t mask, uint64_t total_mem, gp_device_result* out,
                          std::string* err) = 0;
-  // compute processes other than ours on the device right now (0 when unknown): a 16 GiB,
-  // full-SM probe perturbs tenants, so the PERIODIC re-probe skips busy devices
-  virtual int OtherComputeProcs(const std::string& /*uuid*/) { return 0; }
+  // compute processes other than ours on the device right now, -1 when that cannot be told (no NVML):
+  // a 16 GiB, full-SM probe perturbs tenants, so busy devices never get the full probe uninvited
+  virtual int OtherComputeProcs(const std::string& /*uuid*/) { return -1; }
+  // one FULL GPU graded from a fresh child process (CUDA_VISIBLE_DEVICES=<uuid>): a fault in the probe,
+  // or a context already lost to a sticky error, cannot touch the plugin's own process
+  virtual int ProbeIsolated(const std::string& uuid, uint32_t mask, uint64_t total_mem, gp_device_result* out,
+                            std::string* err) { return ProbeSlice(uuid, mask, total_mem, out, err); }
+  // the GPU-to-GPU fabric over the first ngpus CUDA devices (K4); uuids = CUDA ordinal order
+  virtual int ProbeFabric(int /*ngpus*/, gp_fabric_result* /*out*/, std::vector<std::string>* /*uuids*/, std::string* err) {
+    if (err) *err = "fabric probe not available";
+    return GP_ERR_UNSUPPORTED;
+  }
+  // give a kept arena back (Allocate: the pod is about to start) / recover a lost context in-process
+  virtual void TrimDevice(const std::string& /*uuid*/) {}
+  virtual int ResetDevice(const std::string& /*uuid*/) { return GP_ERR_UNSUPPORTED; }
 };
 
 class GpuProbeBackend : public ProbeBackend {
@@ -75,12 +94,27 @@ class GpuProbeBackend : public ProbeBackend {
 
   int OtherComputeProcs(const std::string& uuid) override {
     gp_nvml_info i;
-    if (!ctx_ || gp_nvml_snapshot(ctx_, uuid.c_str(), &i) != GP_OK || !i.available) return 0;
+    if (!ctx_ || gp_nvml_snapshot(ctx_, uuid.c_str(), &i) != GP_OK || !i.available) return -1;
     return (int)i.other_compute_procs;
   }
 
-  // fork + exec the slice binary with CUDA_VISIBLE_DEVICES=<uuid>; it writes the POD result
-  // struct to its stdout.
+  int ProbeFabric(int ngpus, gp_fabric_result* out, std::vector<std::string>* uuids, std::string* err) override {
+    if (!ctx_) { if (err) *err = "gp_init failed: " + init_error_; return rc_ ? rc_ : GP_ERR_CUDA; }
+    const int rc = gp_probe_fabric(ctx_, ngpus, out);
+    if (rc) { if (err) *err = gp_last_error_detail(); return rc; }
+    if (uuids) {
+      uuids->clear();
+      for (int i = 0; i < ngpus; ++i) {
+        char u[64] = "";
+        gp_device_uuid(ctx_, i, u, sizeof(u));
+        uuids->push_back(u);
+      }
+    }
+    return GP_OK;
+  }
+  void TrimDevice(const std::string& uuid) override { if (ctx_) gp_trim_device(ctx_, uuid.c_str()); }
+  int ResetDevice(const std::string& uuid) override { return ctx_ ? gp_device_reset(ctx_, uuid.c_str()) : GP_ERR_CUDA; }
+
   // arrays of a slice probe: the configured size, but never more than a quarter of the slice
   // (triad needs three arrays), rounded down to 1 MiB
   static uint64_t SliceBytes(uint64_t configured, uint64_t total_mem) {
@@ -90,39 +124,76 @@ class GpuProbeBackend : public ProbeBackend {
     return std::max<uint64_t>(want, 1ull << 20);
   }
 
+  // how long a child may take before it is killed and the device reported as not answering
+  void SetChildTimeout(std::chrono::milliseconds t) { child_timeout_ = t; }
+  // extra argv for the child (tests: --test-hang, --test-cuda-error N)
+  void SetChildExtraArgs(std::vector<std::string> a) { child_extra_ = std::move(a); }
+
+  // Spawn the slice binary with CUDA_VISIBLE_DEVICES=<uuid>; it writes the POD result struct to its stdout.
+  // The plugin is heavily multithreaded (CUDA, gRPC): everything the child needs — argv, envp — is built
+  // BEFORE the spawn and the child goes straight to exec (posix_spawn), so nothing between fork and exec can
+  // wait on a lock another thread held.  The pipe is close-on-exec, the read has a deadline, and a child
+  // that does not answer in time is killed and reaped: the caller always gets control back.
   int ProbeSlice(const std::string& uuid, uint32_t mask, uint64_t total_mem, gp_device_result* out, std::string* err) override {
     if (child_.empty()) { if (err) *err = "no slice binary configured"; return GP_ERR_UNSUPPORTED; }
+    const uint64_t hbm = SliceBytes(cfg_.hbm_bytes, total_mem);
+    const uint64_t pat = std::min<uint64_t>(cfg_.pattern_bytes ? cfg_.pattern_bytes : hbm, hbm);
+    std::vector<std::string> args = {child_, std::to_string(mask), std::to_string(hbm), std::to_string(pat),
+                                     std::to_string(cfg_.wo_passes), std::to_string(cfg_.gemm_mnk),
+                                     std::to_string(cfg_.iters), std::to_string(cfg_.warmup)};
+    for (const auto& a : child_extra_) args.push_back(a);
+    std::vector<char*> argv;
+    for (auto& a : args) argv.push_back(const_cast<char*>(a.c_str()));
+    argv.push_back(nullptr);
+    std::vector<std::string> envs;
+    for (char** e = environ; e && *e; ++e)
+      if (strncmp(*e, "CUDA_VISIBLE_DEVICES=", 21) != 0) envs.emplace_back(*e);
+    envs.push_back("CUDA_VISIBLE_DEVICES=" + uuid);
+    std::vector<char*> envp;
+    for (auto& e : envs) envp.push_back(const_cast<char*>(e.c_str()));
+    envp.push_back(nullptr);
+
     int fds[2];
-    if (pipe(fds) != 0) { if (err) *err = "pipe failed"; return GP_ERR_INVALID; }
-    const pid_t pid = fork();
-    if (pid < 0) { close(fds[0]); close(fds[1]); if (err) *err = "fork failed"; return GP_ERR_INVALID; }
-    if (pid == 0) {
-      dup2(fds[1], STDOUT_FILENO);
-      close(fds[0]);
-      close(fds[1]);
-      setenv("CUDA_VISIBLE_DEVICES", uuid.c_str(), 1);
-      const uint64_t hbm = SliceBytes(cfg_.hbm_bytes, total_mem);
-      const uint64_t pat = std::min<uint64_t>(cfg_.pattern_bytes ? cfg_.pattern_bytes : hbm, hbm);
-      const std::string m = std::to_string(mask), hb = std::to_string(hbm),
-                        pb = std::to_string(pat), wo = std::to_string(cfg_.wo_passes),
-                        gm = std::to_string(cfg_.gemm_mnk);
-      execl(child_.c_str(), child_.c_str(), m.c_str(), hb.c_str(), pb.c_str(), wo.c_str(), gm.c_str(), (char*)nullptr);
-      _exit(127);
-    }
+    if (pipe2(fds, O_CLOEXEC) != 0) { if (err) *err = "pipe2 failed"; return GP_ERR_INVALID; }
+    posix_spawn_file_actions_t fa;
+    posix_spawn_file_actions_init(&fa);
+    posix_spawn_file_actions_adddup2(&fa, fds[1], STDOUT_FILENO);  // dup2 clears close-on-exec on the copy
+    pid_t pid = -1;
+    const int sp = posix_spawn(&pid, child_.c_str(), &fa, nullptr, argv.data(), envp.data());
+    posix_spawn_file_actions_destroy(&fa);
     close(fds[1]);
+    if (sp != 0) { close(fds[0]); if (err) *err = "posix_spawn(" + child_ + ") failed: " + strerror(sp); return GP_ERR_INVALID; }
+
+    const auto deadline = std::chrono::steady_clock::now() + child_timeout_;
     size_t got = 0;
     char* dst = reinterpret_cast<char*>(out);
+    bool timed_out = false;
     while (got < sizeof(*out)) {
+      const auto left = std::chrono::duration_cast<std::chrono::milliseconds>(deadline - std::chrono::steady_clock::now()).count();
+      if (left <= 0) { timed_out = true; break; }
+      struct pollfd pfd = {fds[0], POLLIN, 0};
+      const int pr = poll(&pfd, 1, (int)std::min<long long>(left, 1000));
+      if (pr < 0 && errno != EINTR) break;
+      if (pr <= 0) continue;
       const ssize_t n = read(fds[0], dst + got, sizeof(*out) - got);
-      if (n <= 0) break;
+      if (n <= 0) break;  // EOF: the child died before answering
       got += (size_t)n;
     }
     close(fds[0]);
     int status = 0;
+    if (timed_out) kill(pid, SIGKILL);
     waitpid(pid, &status, 0);
+    if (timed_out) {
+      memset(out, 0, sizeof(*out));
+      if (err) *err = "probe process for " + uuid + " did not answer within " + std::to_string(child_timeout_.count()) + " ms and was killed";
+      return GP_ERR_DEVICE_LOST;
+    }
     if (got != sizeof(*out) || out->struct_size != sizeof(*out)) {
-      if (err) *err = "slice probe for " + uuid + " returned no result (exit status " + std::to_string(WIFEXITED(status) ? WEXITSTATUS(status) : -1) + ")";
-      return GP_ERR_CUDA;
+      memset(out, 0, sizeof(*out));
+      const std::string how = WIFSIGNALED(status) ? "killed by signal " + std::to_string(WTERMSIG(status))
+                                                  : "exit status " + std::to_string(WIFEXITED(status) ? WEXITSTATUS(status) : -1);
+      if (err) *err = "probe process for " + uuid + " returned no result (" + how + ")";
+      return GP_ERR_DEVICE_LOST;
     }
     return out->error;
   }
@@ -132,6 +203,8 @@ class GpuProbeBackend : public ProbeBackend {
   gp_ctx* ctx_ = nullptr;
   int rc_ = 0;
   std::string init_error_, child_;
+  std::chrono::milliseconds child_timeout_{120000};
+  std::vector<std::string> child_extra_;
 };
 
 // The new step between building the map and advertising it (device_map.go:34-45 ->
@@ -242,9 +315,12 @@ class NvidiaDevicePlugin {
     std::lock_guard<std::mutex> g(mu_);
     return devices_.GetPluginDevices();
   }
-  // plugin/plugin.go:210-225
+  // plugin/plugin.go:210-225.  New: the devices kubelet is handing to a pod give their kept probe arena back
+  // first (gp_trim_device), so the pod finds the whole memory free.
+  void SetOnAllocate(std::function<void(const std::vector<std::string>&)> f) { on_allocate_ = std::move(f); }
   std::pair<std::string, Error> Allocate(const std::vector<std::string>& ids) const {
     if (!devices_.Contains(ids)) return {"", "invalid allocation request for " + resourceName_};
+    if (on_allocate_) on_allocate_(ids);
     std::string v;
     for (size_t i = 0; i < ids.size(); ++i) v += (i ? "," : "") + ids[i];
     return {"NVIDIA_VISIBLE_DEVICES=" + v, std::nullopt};
@@ -256,6 +332,7 @@ class NvidiaDevicePlugin {
   std::mutex mu_;
   std::condition_variable cv_;
   std::deque<std::pair<std::string, bool>> events_;
+  std::function<void(const std::vector<std::string>&)> on_allocate_;
   bool stop_ = false;
 };
 

@@ -3,7 +3,9 @@
 // CUDA_VISIBLE_DEVICES=MIG-<uuid> before exec: a CUDA process sees a single MIG compute
 // instance at a time, so per-slice probing (device/device_map.go:78-98 visits each slice,
 // device/device.go:32-34 names them "i:j") needs a process per slice, not a thread.
-//   argv: mask hbm_bytes pattern_bytes wo_passes gemm_mnk
+//   argv: mask hbm_bytes pattern_bytes wo_passes gemm_mnk iters warmup [--test-hang] [--test-cuda-error N]
+// The two --test-* switches exist for the parent's own tests: a child that never answers, and a child whose
+// device reports a sticky CUDA fault (injected at the API level, nothing abnormal reaches the GPU).
 #include <unistd.h>
 
 #include <cstdlib>
@@ -21,6 +23,13 @@ int main(int argc, char** argv) {
   if (argc > 3) cfg.pattern_bytes = strtoull(argv[3], nullptr, 10);
   if (argc > 4) cfg.wo_passes = (uint32_t)strtoul(argv[4], nullptr, 10);
   if (argc > 5) cfg.gemm_mnk = (uint32_t)strtoul(argv[5], nullptr, 10);
+  if (argc > 6) cfg.iters = (uint32_t)strtoul(argv[6], nullptr, 10);
+  if (argc > 7) cfg.warmup = (uint32_t)strtoul(argv[7], nullptr, 10);
+  int test_cuda_error = 0;
+  for (int i = 8; i < argc; ++i) {
+    if (!strcmp(argv[i], "--test-hang")) { for (;;) pause(); }
+    if (!strcmp(argv[i], "--test-cuda-error") && i + 1 < argc) test_cuda_error = atoi(argv[++i]);
+  }
   gp_device_result out;
   memset(&out, 0, sizeof(out));
   out.struct_size = sizeof(out);
@@ -28,6 +37,7 @@ int main(int argc, char** argv) {
   gp_ctx* ctx = nullptr;
   int rc = gp_init(&cfg, &ctx);
   if (rc == 0) {
+    if (test_cuda_error) gp_inject_cuda_error(ctx, "0", test_cuda_error);
     rc = gp_probe_device(ctx, "0", mask, &out);
     gp_shutdown(ctx);
   }

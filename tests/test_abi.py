@@ -35,7 +35,7 @@ def test_struct_layout_matches_library():
     assert lib.gp_abi_version() == gpuprobe.GP_ABI_VERSION
     for which, cls in enumerate([gpuprobe.Config, gpuprobe.PatternResult, gpuprobe.Timing,
                                  gpuprobe.GemmResult, gpuprobe.DeviceResult, gpuprobe.KernelStat,
-                                 gpuprobe.NvmlInfo]):
+                                 gpuprobe.NvmlInfo, gpuprobe.FabricResult]):
         assert lib.gp_sizeof(which) == C.sizeof(cls), cls.__name__
     assert lib.gp_sizeof(99) == 0
     assert C.sizeof(gpuprobe.PatternResult) == 48  # "result struct 48 B per pass"

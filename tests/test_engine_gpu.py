@@ -98,3 +98,85 @@ def test_whole_memory_grading():
         assert r.healthy == 1 and r.pattern_passes == 4 and r.pattern_mismatches == 0
         assert r.pattern_bytes > (100 << 30) and r.pattern_bytes % (1 << 20) == 0  # most of the 180 GB card
         assert r.verify_gbps_best > 1000 and r.fill_gbps_best > 1000
+
+
+@pytest.mark.parametrize("backend", [gpuprobe.GP_ARENA_VMM, gpuprobe.GP_ARENA_MALLOC], ids=["vmm", "cudaMalloc"])
+def test_arena_time_is_reported_and_a_kept_arena_costs_nothing(backend):
+    """gp_device_result says where the call's time went.  keep_arena = 0: every call grows and releases the
+    arena (alloc_s, free_s > 0).  keep_arena = 1 (the periodic re-probe of an idle device): the second call
+    finds the arena in place — no allocation inside the call — until gp_trim_device hands it back."""
+    mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_PATTERN
+    kw = dict(hbm_bytes=1 << 30, wo_passes=2, iters=2, warmup=1, arena_backend=backend)
+    with gpuprobe.Probe(keep_arena=0, **kw) as p:
+        for _ in range(2):
+            r = p.probe_device("0", mask)
+            assert r.healthy == 1 and r.arena_backend == backend and r.arena_reused == 0
+            assert r.alloc_s > 0 and r.free_s > 0 and r.arena_bytes >= 2 << 30
+            assert abs(r.duration_s - (r.alloc_s + r.free_s + r.kernels_s)) < 1e-9
+    with gpuprobe.Probe(keep_arena=1, **kw) as p:
+        first = p.probe_device("0", mask)
+        again = p.probe_device("0", mask)
+        assert first.alloc_s > 0 and first.arena_reused == 0 and first.free_s == 0
+        assert again.alloc_s == 0 and again.free_s == 0 and again.arena_reused == 1 and again.healthy == 1
+        # growing a kept arena maps only the difference and leaves the lower part where it was
+        p.pattern_fill("0", gpuprobe.GP_PAT_ADDRESS, 0, (1 << 30) // 8)
+        p.pattern_fill("0", gpuprobe.GP_PAT_WALKING_ONES, 5, (3 << 30) // 8)
+        assert p.pattern_verify("0", gpuprobe.GP_PAT_WALKING_ONES, 5, (3 << 30) // 8).mismatches == 0
+        p.trim_device("0")   # what the plugin calls from Allocate(): the pod gets the memory back
+        after = p.probe_device("0", mask)
+        assert after.arena_reused == 0 and after.alloc_s > 0 and after.healthy == 1
+
+
+def test_sm_limit_runs_the_launchers_at_slice_scale():
+    """A 1g MIG slice exposes ~1/7 of the SMs and 23 GiB: the grids and the arena must size themselves to
+    what the device reports.  gp_config.sm_limit makes the launchers believe in 18 SMs (9 CTA pairs)."""
+    with gpuprobe.Probe(hbm_bytes=256 << 20, wo_passes=2, iters=2, warmup=1, gemm_mnk=2048, sm_limit=18) as p:
+        r = p.probe_device("0", gpuprobe.GP_PROBE_ALL_SINGLE)
+        assert r.healthy == 1 and r.sm_count == 18 and r.gemm.samples_bad == 0
+        full = gpuprobe.Probe(hbm_bytes=256 << 20, gemm_mnk=2048, iters=2, warmup=1)
+        g_full = full.gemm_probe("0", mnk=2048, iters=3, warmup=1, samples=256)
+        full.close()
+        g = p.gemm_probe("0", mnk=2048, iters=3, warmup=1, samples=256)
+        assert g.samples_bad == 0 and g.tflops_best < 0.5 * g_full.tflops_best  # really ran on fewer CTAs
+    with gpuprobe.Probe(sm_limit=1, gemm_mnk=512, gemm_variant=gpuprobe.GP_GEMM_AUTO) as p:  # odd / tiny counts
+        assert p.gemm_probe("0", mnk=512, iters=1, warmup=0, samples=64).samples_bad == 0
+
+
+_POISON_SCRIPT = r"""
+import sys
+sys.path.insert(0, sys.argv[1])
+import gpuprobe
+p = gpuprobe.Probe(hbm_bytes=64 << 20, wo_passes=1, iters=1, warmup=1)
+dev = p.device_uuid(0)
+mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_PATTERN
+assert p.probe_device(dev, mask).healthy == 1
+assert not p.device_poisoned(dev)
+# a non-sticky error (2 = cudaErrorMemoryAllocation) is reported and forgotten
+assert p.inject_cuda_error(dev, 2) == gpuprobe.GP_ERR_NOMEM and not p.device_poisoned(dev)
+# a sticky one (700 = cudaErrorIllegalAddress) loses the device for this process
+assert p.inject_cuda_error(dev, 700) == gpuprobe.GP_ERR_DEVICE_LOST and p.device_poisoned(dev)
+for call in (lambda: p.probe_device(dev, mask), lambda: p.pattern_fill(dev, 0, 0, 64)):
+    try:
+        call()
+        raise SystemExit("a call on a lost device succeeded")
+    except gpuprobe.GpuProbeError as e:
+        assert e.code == gpuprobe.GP_ERR_DEVICE_LOST, e
+        assert "gp_device_reset" in e.detail
+p.device_reset(dev)            # in-process recovery: only for hosts where nothing else uses CUDA
+assert not p.device_poisoned(dev)
+r = p.probe_device(dev, mask)
+assert r.healthy == 1 and r.alloc_s > 0
+p.close()
+print("poison-reset ok")
+"""
+
+
+def test_sticky_fault_marks_the_device_lost_and_reset_recovers(tmp_path):
+    """Runs in a child process (gp_device_reset is cudaDeviceReset: it would take this pytest process's
+    torch context with it).  The fault itself is injected at the API level — nothing abnormal reaches the GPU."""
+    import os
+    import subprocess
+    import sys
+    pkg = os.path.dirname(os.path.dirname(gpuprobe.__file__))
+    r = subprocess.run([sys.executable, "-c", _POISON_SCRIPT, pkg], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "poison-reset ok" in r.stdout, (r.stdout, r.stderr)

@@ -46,3 +46,31 @@ def test_plugin_sim_floor_makes_device_unhealthy():
     assert d["unhealthy"] == d["devices"]
     assert all(x["health"] == "Unhealthy" for x in d["lists"][0])  # kubelet never sees it Healthy
     assert "failed_mask=1" in d["log"][0]
+
+
+def test_manager_scenario_fabric_and_isolation():
+    """PluginManager on real GPUs: grade + fabric inside loadPlugins, then the isolated re-probe path: a child
+    whose device reports a sticky fault, a child that never answers (killed at the deadline), and the way back
+    to Healthy each time, with the plugin's own process and context untouched."""
+    d = run_sim("--scenario", "manager", "--slice", os.path.join(HOST, "gpuprobe-slice"), "--fabric-mib", "64")
+    assert d["devices"] >= 1 and d["unhealthy"] == 0
+    steps = {s["step"]: s for s in d["steps"]}
+    assert steps["isolated"]["verdict"] == "Healthy" and steps["isolated"]["error"] == 0
+    assert steps["child_fault"]["verdict"] == "Unhealthy" and steps["child_fault"]["error"] == -9   # GP_ERR_DEVICE_LOST
+    assert steps["after_fault"]["verdict"] == "Healthy"
+    assert steps["child_hang"]["verdict"] == "Unhealthy" and steps["child_hang"]["error"] == -9
+    assert steps["after_hang"]["verdict"] == "Healthy" and steps["in_process"]["verdict"] == "Healthy"
+    assert d["isolated_probes"] == 5
+    # kubelet saw: all Healthy, then down/up for the fault, down/up for the hang
+    first_id = d["lists"][0][0]["ID"]
+    seq = [next(x["health"] for x in l if x["ID"] == first_id) for l in d["lists"]]
+    assert seq == ["Healthy", "Unhealthy", "Healthy", "Unhealthy", "Healthy"]
+    assert any("did not answer within 1500 ms and was killed" in l for l in d["log"])
+    if d["devices"] >= 2:
+        f = d["fabric"]
+        assert f["ngpus"] == d["devices"] and f["healthy"] == 1 and f["data_ok"] == 1
+        assert 100 < f["read_min"] <= f["read_max"] < 1000 and 100 < f["write_min"] <= f["write_max"] < 1000
+        assert f["allreduce_error"] in (0, -4)   # NCCL may be absent outside the python process
+        assert len(d["preferred"]) == 2
+        assert 'gpu_probe_p2p_gbps{dir=\"read\",dst=\"1\",src=\"0\"}' in d["metrics"] or "gpu_probe_p2p_gbps{dir=\"read\"" in d["metrics"]
+        assert "gpu_probe_fabric_healthy" in d["metrics"]

@@ -61,7 +61,7 @@ def test_p2p_matrix_pairs(mp):
     n = mp.device_count()
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
-    for direction in (0, 1, 2, 4):
+    for direction in (0, 1, 2, 4, 5, 6):  # 5, 6: the cudaMemcpyPeerAsync yardstick, same schedule
         m = mp.probe_p2p(n, 256 << 20, direction)
         off = [m[i][j] for i in range(n) for j in range(n) if i != j]
         assert min(off) > 100, (direction, m)          # NVLink, not PCIe
@@ -81,3 +81,40 @@ def test_allreduce_pairs(mp):
     alg, bus = mp.probe_allreduce(n, 256 << 20, warmup=2, iters=5)
     assert abs(bus - alg * 2 * (n - 1) / n) < 1e-6 * max(bus, 1)
     assert bus > 50
+
+
+def test_p2p_every_mode_checks_its_data_on_one_gpu(mp):
+    """The diagonal runs the same kernels on local memory; every read folds what it loaded and the host
+    compares it with the closed form of the address pattern (a read that returned garbage at full speed
+    would otherwise grade healthy), every write and copy is verified where it landed."""
+    for direction in (gpuprobe.GP_P2P_READ, gpuprobe.GP_P2P_WRITE, gpuprobe.GP_P2P_COPY_ENGINE):
+        for nbytes in (64 << 10, 1 << 20, (16 << 20) + 32):   # the last one is ragged for every launch shape
+            m = mp.probe_p2p(1, nbytes, direction)
+            assert m[0][0] > 0
+
+
+def test_fabric_verdict_single_gpu_and_floors(mp):
+    f = mp.probe_fabric(1)
+    assert f.healthy == 1 and f.data_ok == 1 and f.failed == 0 and f.ngpus == 1
+    assert f.read_gbps[0] > 500 and f.write_gbps[0] > 500 and f.worst_src == -1
+    with pytest.raises(gpuprobe.GpuProbeError):
+        mp.probe_fabric(gpuprobe.GP_FABRIC_MAX_GPUS + 1)
+
+
+def test_fabric_verdict_pairs():
+    """On >= 2 GPUs: flat NVSwitch matrix, floors enforced in both directions of the comparison."""
+    import torch  # noqa: F401  (NCCL soname, see the fixture above)
+    with gpuprobe.Probe(keep_arena=1, fabric_bytes=256 << 20) as p:
+        n = p.device_count()
+        if n < 2:
+            pytest.skip("needs >= 2 GPUs")
+        f = p.probe_fabric(n)
+        assert f.healthy == 1 and f.data_ok == 1
+        assert 100 < f.read_min <= f.read_max < 1000 and 100 < f.write_min <= f.write_max < 1000
+        assert 1.0 <= f.spread < 1.5 and f.worst_gbps == min(f.read_min, f.write_min)
+        assert f.allreduce_error == 0 and f.allreduce_busbw_gbps > 50
+    # a floor no fabric can meet: the same measurement must now grade unhealthy, with the reason bits set
+    with gpuprobe.Probe(keep_arena=1, fabric_bytes=64 << 20, min_p2p_gbps=5000.0, max_p2p_spread=1.0000001,
+                        min_allreduce_busbw_gbps=1e6) as p:
+        f = p.probe_fabric(n)
+        assert f.healthy == 0 and (f.failed & 1) and (f.failed & 4) and f.data_ok == 1

@@ -31,7 +31,7 @@ def _run(torch, host_words, kind, pas):
     return tuple(int(v) & M64 for v in d_res.cpu().numpy().view(np.uint64))
 
 
-def test_noalloc_matches_existing_entry_point_twice_in_a_row(probe):
+def test_noalloc_matches_existing_entry_point_twice_in_a_row(probe, oracle):
     import torch
     torch.cuda.set_device(0)
     n = 64 * 5000 + 64  # not a multiple of the 4096-word chunk: exercises the ragged last CTA
@@ -50,8 +50,42 @@ def test_noalloc_matches_existing_entry_point_twice_in_a_row(probe):
     ref2 = probe.pattern_host("0", words2, gpuprobe.GP_PAT_ADDRESS, 1, fill=False).astuple()
     assert got1 == ref1  # bit-exact, as every integer test in this suite
     assert got2 == ref2
+    # and both against the CPU oracle on the same words, not only against the other CUDA entry point
+    import oracle_lib
+    assert got1 == oracle_lib.verify(oracle, words1, gpuprobe.GP_PAT_WALKING_ONES, 9).astuple()
+    assert got2 == oracle_lib.verify(oracle, words2, gpuprobe.GP_PAT_ADDRESS, 1).astuple()
     assert got1[3:] == (2, 777, 1 << 40)
     assert got2[3:] == (0, M64, 0)
+
+
+def test_noalloc_grades_a_sub_range_and_refuses_misaligned_pointers(oracle):
+    """A caller grading part of its own buffer passes an interior pointer.  The kernels load 256 bits at
+    a time, so the range has to start on a 32-byte boundary: an aligned interior pointer works, anything
+    else is refused with GP_ERR_INVALID before a kernel could fault on it (a misaligned-address fault is
+    sticky and would take the caller's whole context down)."""
+    import torch
+    import oracle_lib
+    torch.cuda.set_device(0)
+    n = 64 * 100
+    i = np.arange(n, dtype=np.uint64)
+    words = np.left_shift(np.uint64(1), (i + np.uint64(3)) & np.uint64(63))
+    words[2000] ^= np.uint64(1 << 7)
+    big = torch.zeros(n + 64, dtype=torch.int64, device="cuda")
+    big[4:4 + n] = torch.from_numpy(words.view(np.int64)).cuda()       # +32 bytes: still aligned
+    d_res = torch.full((8,), -1, dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    gpuprobe.pattern_verify_noalloc(0, big.data_ptr() + 32, n, gpuprobe.GP_PAT_WALKING_ONES, 3,
+                                    d_res.data_ptr() + 8, stream)      # result slot at +8: still aligned
+    torch.cuda.synchronize()
+    got = tuple(int(v) & M64 for v in d_res[1:7].cpu().numpy().view(np.uint64))
+    assert got == oracle_lib.verify(oracle, words, gpuprobe.GP_PAT_WALKING_ONES, 3).astuple()
+    assert got[3:] == (1, 2000, 1 << 7)
+    for woff, roff in [(8, 0), (16, 0), (0, 4), (24, 4)]:
+        with pytest.raises(gpuprobe.GpuProbeError) as e:
+            gpuprobe.pattern_verify_noalloc(0, big.data_ptr() + woff, 64, gpuprobe.GP_PAT_WALKING_ONES, 0,
+                                            d_res.data_ptr() + roff, stream)
+        assert e.value.code == gpuprobe.GP_ERR_INVALID and "aligned" in e.value.detail
+    torch.cuda.synchronize()  # the refused calls launched nothing: the context is intact
 
 
 def test_noalloc_rejects_oversize_and_bad_arguments():
