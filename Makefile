@@ -12,7 +12,7 @@ HDRS := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/gpuprobe.h
 HOST := $(PKG)/host
 HOST_HDRS := $(wildcard $(HOST)/*.hpp) include/gpuprobe.h
 CXX ?= g++
-CXXFLAGS := -O2 -std=c++17 -Wall -Wextra -pthread
+CXXFLAGS := -O2 -g -std=c++17 -Wall -Wextra -pthread -rdynamic
 
 all: $(LIB) oracle host
 

@@ -222,12 +222,16 @@ typedef struct gp_device_result {
   uint64_t pattern_digest;  /* checksum of checksums: SUM over passes of (sum ^ rotl(xor,1) ^ rotl(wsum,2)) * (pass_no+1) */
   gp_gemm_result gemm;
   /* ---- ABI 2: where duration_s went (host steady_clock) ---- */
-  double alloc_s;           /* growing the arena inside this call (0 when the kept arena was large enough) */
-  double free_s;            /* releasing it before return (keep_arena = 0 only) */
+  double alloc_s;           /* host time this call spent WAITING for memory: growing the arena, minus whatever part of
+                             * that ran on the helper thread behind the GEMM probe (0 when the kept arena was large enough) */
+  double free_s;            /* releasing it before return; 0 when the release was handed to the reaper thread */
   double kernels_s;         /* duration_s - alloc_s - free_s: generation, warm-up, timed launches, checks, copies */
   uint64_t arena_bytes;     /* device memory the call ran in */
   uint32_t arena_reused;    /* 1 if the arena was already there on entry (periodic re-probe of an idle device) */
   uint32_t arena_backend;   /* GP_ARENA_VMM or GP_ARENA_MALLOC actually used */
+  uint32_t free_deferred;   /* 1 if keep_arena = 0 and the arena is being released on a background thread as the call
+                             * returns (the memory is back with the driver a moment later; the next call waits for it) */
+  uint32_t reserved3;
 } gp_device_result;
 
 /* Verdict on the GPU-to-GPU fabric (K4 of SURVEY.md §8): the P2P matrices, their spread, the worst pair and the

@@ -2,19 +2,23 @@
 //
 // No reference counterpart (the reference never allocates device memory).  Two backends:
 //
-//   VMM (default): one virtual range per device is reserved on first use (cuMemAddressReserve; virtual
-//   space is free) and physical chunks (cuMemCreate, 1 GiB each plus one tail chunk) are mapped from
-//   its base upwards as the arena grows.  Growing never moves what is already mapped, so a kept arena
-//   (keep_arena = 1, the periodic re-probe of an idle device) costs nothing inside the probe call and
-//   a larger request only maps the difference.  gp_trim / gp_trim_device unmap and release the
-//   physical memory (pods get it back) but keep the reservation.
+//   VMM (AUTO's choice with keep_arena = 1): one virtual range per device is reserved on first use
+//   (cuMemAddressReserve; virtual space is free) and physical chunks (cuMemCreate, 4 GiB each plus one
+//   tail chunk) are mapped from its base upwards as the arena grows.  Growing never moves what is
+//   already mapped, so a kept arena (the periodic re-probe of an idle device) costs nothing inside the
+//   probe call and a larger request only maps the difference.  gp_trim / gp_trim_device unmap and
+//   release the physical memory (pods get it back) but keep the reservation.
 //
-//   cudaMalloc: one allocation per size change, as in round 1 (kept for devices / drivers without
-//   VMM support and as the A/B baseline; gp_config.arena_backend selects).
+//   cudaMalloc (AUTO's choice with keep_arena = 0): one allocation per size change.  Measured
+//   (profiles/arena_timing_r02.txt): it is the cheapest way to get and return 48 GiB cold — 5 ms +
+//   11..19 ms against 12 + 35 ms for VMM in 4 GiB chunks; the VMM calls cost 0.2 - 1 ms EACH.
 //
-// Measured reason (SCALE_r01): cudaMalloc + cudaFree of 48 GiB inside every
-// gp_probe_device call cost ~55 ms alone and ~225 ms when eight processes did it at once (the
-// driver serialises memory management across processes); Device::alloc_s / free_s now report it.
+// Either way the driver serialises memory management across threads and processes (eight processes
+// freeing 48 GiB at once: 225 ms, SCALE_r01), so what cannot be avoided is taken off the caller's
+// path: a cold probe hands its arena to a reaper thread and returns (free_arena_deferred; the next
+// call on the device joins it first), and gp_probe_device grows the big arena on a helper thread
+// while the GEMM probe runs in a small buffer of its own.  Device::alloc_s / free_s report the host
+// time the call really spent blocked on the allocator.
 #include <cuda.h>
 
 #include <chrono>
@@ -62,7 +66,8 @@ const VmmApi* vmm_api() {
   return &api;
 }
 
-constexpr size_t kChunkBytes = 1ull << 30;
+constexpr size_t kChunkBytes = 4ull << 30;
+constexpr size_t kVaAlign = 1ull << 30;
 
 int cu_fail(CUresult r, const char* what) {
   set_error("%s failed: CUresult %d", what, (int)r);
@@ -88,16 +93,17 @@ CUmemAccessDesc access_for(int ordinal) {
   return a;
 }
 
-// unmap + release everything mapped above `keep_bytes` (a chunk boundary); VMM backend only
+// unmap + release everything mapped above `keep_bytes` (a chunk boundary); VMM backend only.  One
+// cuMemUnmap covers all the chunks being dropped (measured: 3 ms against 17 ms chunk by chunk).
 void vmm_shrink(Device* d, size_t keep_bytes) {
   const VmmApi* api = vmm_api();
   size_t off = d->arena_bytes;
-  while (!d->chunks.empty() && off > keep_bytes) {
-    const Device::Chunk c = d->chunks.back();
-    off -= c.bytes;
-    api->Unmap((CUdeviceptr)(d->va_base + off), c.bytes);
-    api->Release((CUmemGenericAllocationHandle)c.handle);
-    d->chunks.pop_back();
+  size_t first = d->chunks.size();
+  while (first > 0 && off > keep_bytes) { off -= d->chunks[first - 1].bytes; --first; }
+  if (first < d->chunks.size()) {
+    api->Unmap((CUdeviceptr)(d->va_base + off), d->arena_bytes - off);
+    for (size_t i = first; i < d->chunks.size(); ++i) api->Release((CUmemGenericAllocationHandle)d->chunks[i].handle);
+    d->chunks.resize(first);
   }
   d->arena_bytes = off;
   if (off == 0) { d->arena = nullptr; d->peer_mask = 0; }
@@ -117,7 +123,7 @@ int vmm_grow(Ctx* ctx, Device* d, size_t bytes) {
     // everything the device could ever hold, rounded up: virtual space costs nothing
     size_t va = ((size_t)d->total_mem + 2 * kChunkBytes - 1) / kChunkBytes * kChunkBytes;
     CUdeviceptr base = 0;
-    r = api->AddressReserve(&base, va, kChunkBytes, 0, 0);
+    r = api->AddressReserve(&base, va, kVaAlign, 0, 0);
     if (r != CUDA_SUCCESS) return cu_fail(r, "cuMemAddressReserve");
     d->va_base = (unsigned long long)base;
     d->va_bytes = va;
@@ -151,6 +157,7 @@ int vmm_grow(Ctx* ctx, Device* d, size_t bytes) {
 
 bool want_vmm(const Ctx* ctx, const Device* d) {
   if (ctx->cfg.arena_backend == GP_ARENA_MALLOC) return false;
+  if (ctx->cfg.arena_backend == GP_ARENA_AUTO && !ctx->cfg.keep_arena) return false;  // cold every call: cudaMalloc is cheaper
   static bool supported[64] = {};
   static bool known[64] = {};
   if (!vmm_api()->ok || d->ordinal < 0 || d->ordinal >= 64) return false;
@@ -170,7 +177,43 @@ uint64_t cfg_arena_cap(const Ctx* c) {
   return c->cfg.arena_cap_bytes ? c->cfg.arena_cap_bytes : 5 * hbm + (1ull << 30);
 }
 
+void arena_join_reaper(Device* d) {
+  if (d->reaper.joinable()) d->reaper.join();
+}
+
+// Release the arena on a background thread and return at once: the caller's results are complete, what is left
+// is handing memory back, and the driver takes tens to hundreds of milliseconds over that when several GPUs do it
+// together.  The memory is back with the driver when the thread ends; anything on this device that needs the
+// allocator again (ensure_arena, free_arena, trim, reset, shutdown) joins it first.
+void free_arena_deferred(Device* d) {
+  arena_join_reaper(d);
+  if (!d->arena) { d->arena_bytes = 0; d->triad_operands_bytes = 0; return; }
+  uint8_t* arena = d->arena;
+  const bool vmm = d->arena_is_vmm;
+  const unsigned long long va = d->va_base;
+  const size_t bytes = d->arena_bytes;
+  std::vector<Device::Chunk> chunks;
+  chunks.swap(d->chunks);
+  const int ordinal = d->ordinal;
+  d->arena = nullptr;
+  d->arena_bytes = 0;
+  d->peer_mask = 0;
+  d->triad_operands_bytes = 0;
+  d->reaper = std::thread([=] {
+    cudaSetDevice(ordinal);
+    if (vmm) {
+      const VmmApi* api = vmm_api();
+      api->Unmap((CUdeviceptr)va, bytes);
+      for (const auto& c : chunks) api->Release((CUmemGenericAllocationHandle)c.handle);
+    } else {
+      cudaFree(arena);
+    }
+    (void)cudaGetLastError();
+  });
+}
+
 void free_arena(Device* d) {
+  arena_join_reaper(d);
   if (!d->arena) { d->arena_bytes = 0; d->triad_operands_bytes = 0; return; }
   Stopwatch sw;
   cudaSetDevice(d->ordinal);
@@ -201,6 +244,7 @@ int ensure_arena(Ctx* ctx, Device* d, size_t bytes, bool ignore_cap) {
     return GP_ERR_NOMEM;
   }
   Stopwatch sw;
+  arena_join_reaper(d);  // memory on its way back to the driver must have arrived before asking for more
   const bool vmm = want_vmm(ctx, d);
   if (d->arena && d->arena_is_vmm != vmm) free_arena(d);
   if (!vmm) free_arena(d);  // cudaMalloc cannot grow in place

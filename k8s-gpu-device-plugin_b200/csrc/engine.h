@@ -8,9 +8,11 @@
 #include <cuda_runtime.h>
 
 #include <cstdlib>
+#include <functional>
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/gpuprobe.h"
@@ -41,6 +43,7 @@ struct Device {
   std::vector<Chunk> chunks;
   unsigned long long peer_mask = 0;         // ordinals (bit i) that have been granted access to the mapped range
   double alloc_s = 0, free_s = 0;           // host seconds spent growing / releasing since the caller last zeroed them
+  std::thread reaper;                       // deferred release of the last arena (free_arena_deferred)
   bool poisoned = false;                    // a sticky CUDA fault was seen: context dead until gp_device_reset
   int poison_code = 0;                      // the cudaError_t that did it
   uint8_t* scratch = nullptr;               // kVerifyScratchBytes | results | counters
@@ -82,6 +85,8 @@ Device* find_device(Ctx* ctx, const char* uuid);
 int device_prepare(Ctx* ctx, Device* d);                  // lazy per-device init, lock held
 int ensure_arena(Ctx* ctx, Device* d, size_t bytes, bool ignore_cap = false);  // lock held
 void free_arena(Device* d);
+void free_arena_deferred(Device* d);         // same, on a reaper thread; returns at once
+void arena_join_reaper(Device* d);
 void release_arena_va(Device* d);            // at shutdown / reset: give the virtual range back too
 // make d's mapped arena readable and writable from the devices in `ordinal_mask` (VMM memory is not
 // covered by cudaDeviceEnablePeerAccess); a no-op for a cudaMalloc arena
@@ -99,7 +104,9 @@ void summarize(const std::vector<float>& ms, gp_timing* t);
 
 // implemented in gemm.cu / p2p.cu
 int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t warmup,
-                      uint32_t iters, uint32_t samples, gp_gemm_result* out);
+                      uint32_t iters, uint32_t samples, gp_gemm_result* out, uint8_t* workspace = nullptr,
+                      const std::function<void()>* after_timed = nullptr);
+size_t gemm_probe_bytes(const Ctx* ctx, uint32_t mnk, uint32_t samples);
 int gemm_host_locked(Ctx* ctx, Device* d, const uint16_t* a, const uint16_t* b, float* c,
                      uint32_t m, uint32_t n, uint32_t k);
 int p2p_probe(Ctx* ctx, int ngpus, size_t bytes, int dir, double* gbps);

@@ -31,6 +31,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <thread>
 #include <vector>
 
@@ -694,8 +695,21 @@ __global__ void unwrite_tile_kernel(T* __restrict__ C, int N, int row0, int col0
   C[(size_t)(row0 + r) * N + col0 + c] = v;
 }
 
+size_t gemm_probe_bytes(const Ctx* ctx, uint32_t mnk, uint32_t samples) {
+  const bool out_bf16 = ctx->cfg.gemm_output == 1;
+  auto up = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
+  const size_t ab = 2 * up((size_t)mnk * mnk * 2), c32 = up((size_t)mnk * mnk * 4), c16 = out_bf16 ? up((size_t)mnk * mnk * 2) : 0;
+  const size_t vec_bytes = up((size_t)mnk * sizeof(double));
+  if (samples > 65536) samples = 65536;
+  return ab + c32 + c16 + 7 * vec_bytes + up((size_t)samples * 8) + up((size_t)samples * 4);
+}
+
+// workspace != nullptr: run in that buffer (gemm_probe_bytes long) instead of the arena.  after_timed, if given, is
+// called once the timed launches have completed: gp_probe_device starts allocating the big arena there, behind
+// the checks (device-side Freivalds, host-side fp64 samples) and clear of the launches being timed
 int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t warmup, uint32_t iters,
-                      uint32_t samples, gp_gemm_result* out) {
+                      uint32_t samples, gp_gemm_result* out, uint8_t* workspace,
+                      const std::function<void()>* after_timed) {
   memset(out, 0, sizeof(*out));
   out->struct_size = (uint32_t)sizeof(*out);
   int rc = check_device(d);
@@ -711,10 +725,13 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
   auto up = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
   const size_t vec_bytes = up((size_t)std::max(std::max(m, n), k) * sizeof(double));
   const size_t aux = 7 * vec_bytes + up((size_t)samples * 8) + up((size_t)samples * 4);
-  rc = ensure_arena(ctx, d, up(a_bytes) + up(b_bytes) + up(c32_bytes) + up(c16_bytes) + aux);
-  if (rc) return rc;
-  d->triad_operands_bytes = 0;
-  uint8_t* p = d->arena;
+  uint8_t* p = workspace;
+  if (!p) {
+    rc = ensure_arena(ctx, d, up(a_bytes) + up(b_bytes) + up(c32_bytes) + up(c16_bytes) + aux);
+    if (rc) return rc;
+    d->triad_operands_bytes = 0;
+    p = d->arena;
+  }
   uint16_t* A = reinterpret_cast<uint16_t*>(p); p += up(a_bytes);
   uint16_t* B = reinterpret_cast<uint16_t*>(p); p += up(b_bytes);
   float* C32 = reinterpret_cast<float*>(p); p += up(c32_bytes);
@@ -744,6 +761,10 @@ int gemm_probe_locked(Ctx* ctx, Device* d, uint32_t mnk, uint64_t seed, uint32_t
     CU_OR_RETURN(launch_gemm(plan, out_bf16, Ctimed, m, n, k, d->sm_count, s));
   }
   CU_OR_RETURN(cudaEventRecord(d->events[iters], s));
+  if (after_timed) {  // the timed launches are over: from here on the caller may keep the allocator busy on this device
+    CU_OR_RETURN(cudaStreamSynchronize(s));
+    (*after_timed)();
+  }
   // with bf16 output the strict checks run on the fp32 C of the same plan (one more launch, untimed), and the
   // bf16 C must equal its rounding bit for bit
   if (out_bf16) CU_OR_RETURN(launch_gemm(plan, false, C32, m, n, k, d->sm_count, s));

@@ -15,9 +15,11 @@ constexpr int kPatNone = 3;
 // partials into slot (blockIdx & (kVerifySlots-1)); 64-byte stride keeps slots in separate
 // L2 sectors so the reductions spread over the L2 slices.
 struct VerifySlot {
-  uint64_t sum, xor_, wsum, mismatches, first_bad_index;
-  uint64_t pad[3];
+  uint64_t sum, xor_, wsum, mismatches;
+  uint64_t first_bad_index, first_bad_xor;  // one 16-byte pair at offset 32: updated together by a 128-bit CAS
+  uint64_t pad[2];
 };
+static_assert(sizeof(VerifySlot) == 64, "one slot per 64 bytes");
 constexpr int kVerifySlots = 512;
 // scratch layout: [kVerifySlots] VerifySlot.  Rest state: sums 0, first_bad_index all-ones
 // (set once by launch_verify_scratch_init, restored by every verify launch's finalize CTA).

@@ -57,6 +57,29 @@ Nvml* nvml() {
   return &n;
 }
 
+// does THIS process hold an active primary context on the device (ours, or anybody else's in the process)?
+bool self_has_context(int ordinal) {
+  typedef int (*GetDevFn)(int*, int);
+  typedef int (*StateFn)(int, unsigned int*, int*);
+  static GetDevFn get_dev = nullptr;
+  static StateFn state = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuDeviceGet", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      get_dev = reinterpret_cast<GetDevFn>(p);
+    if (cudaGetDriverEntryPoint("cuDevicePrimaryCtxGetState", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      state = reinterpret_cast<StateFn>(p);
+    (void)cudaGetLastError();
+  });
+  if (!get_dev || !state) return false;
+  int dev = 0, active = 0;
+  unsigned int flags = 0;
+  if (get_dev(&dev, ordinal) != 0 || state(dev, &flags, &active) != 0) return false;
+  return active != 0;
+}
+
 }  // namespace
 
 extern "C" int gp_nvml_snapshot(gp_ctx* ctx, const char* uuid, gp_nvml_info* out) {
@@ -86,9 +109,16 @@ extern "C" int gp_nvml_snapshot(gp_ctx* ctx, const char* uuid, gp_nvml_info* out
     unsigned int count = 64;
     const nvmlReturn_t rc = n->GetProcs(h, &count, infos);
     if (rc == 0) {
+      // "Other" must not count this process.  NVML reports pids of the HOST pid namespace; in a pod without
+      // hostPID getpid() is a different number and the caller would see itself as a tenant on every GPU it has
+      // ever touched (and never grade it again).  So: drop our pid if it is in the list; if it is not, but this
+      // process holds an active primary context on the device, exactly one of the listed processes is us.
       const unsigned int self = (unsigned int)getpid();
-      for (unsigned int i = 0; i < count && i < 64; ++i)
-        if (infos[i].pid != self) out->other_compute_procs++;
+      bool found_self = false;
+      for (unsigned int i = 0; i < count && i < 64; ++i) found_self = found_self || infos[i].pid == self;
+      unsigned int others = count;
+      if (found_self || (count > 0 && self_has_context(d->ordinal))) others -= 1;
+      out->other_compute_procs = others;
     } else if (rc == 7 /* NVML_ERROR_INSUFFICIENT_SIZE */) {
       out->other_compute_procs = count;
     }

@@ -43,11 +43,34 @@ pattern_fill_kernel(uint64_t* __restrict__ words, uint64_t nvec, int pass) {
 }
 
 struct Acc {
-  uint64_t sum, xr, wsum, mism, first_idx;
+  uint64_t sum, xr, wsum, mism, first_idx, first_xor;  // first_xor = w ^ P at first_idx, captured when it was seen
 };
 
 __device__ __forceinline__ void acc_init(Acc& a) {
-  a.sum = 0; a.xr = 0; a.wsum = 0; a.mism = 0; a.first_idx = ~0ull;
+  a.sum = 0; a.xr = 0; a.wsum = 0; a.mism = 0; a.first_idx = ~0ull; a.first_xor = 0;
+}
+
+// {index, xor} pair <- mine if my index is lower: a 128-bit compare-and-swap loop (cold path only: a warp
+// comes here once per launch, and only if it saw a mismatch).  The xor therefore always belongs to the index
+// it is stored with, and it is the value seen when the word was read — a transient fault that a later re-read
+// would no longer show is still reported with the bits that were wrong.
+__device__ __forceinline__ void first_bad_min(VerifySlot* s, uint64_t idx, uint64_t xr) {
+  uint64_t oi = *reinterpret_cast<volatile uint64_t*>(&s->first_bad_index);
+  uint64_t ox = *reinterpret_cast<volatile uint64_t*>(&s->first_bad_xor);
+  while (idx < oi) {
+    uint64_t gi, gx;
+    asm volatile(
+        "{\n\t.reg .b128 c, n, o;\n\t"
+        "mov.b128 c, {%3, %4};\n\t"
+        "mov.b128 n, {%5, %6};\n\t"
+        "atom.global.cas.b128 o, [%2], c, n;\n\t"
+        "mov.b128 {%0, %1}, o;\n\t}"
+        : "=l"(gi), "=l"(gx)
+        : "l"(&s->first_bad_index), "l"(oi), "l"(ox), "l"(idx), "l"(xr)
+        : "memory");
+    if (gi == oi && gx == ox) break;
+    oi = gi; ox = gx;
+  }
 }
 
 // word-by-word compare of one vector; only reached when the vector is known to differ (or on
@@ -56,20 +79,22 @@ __device__ __forceinline__ void acc_init(Acc& a) {
 template <int KIND>
 __device__ __noinline__ uint64_t compare_words_slow(uint64_t w0, uint64_t w1, uint64_t w2,
                                                     uint64_t w3, uint64_t i, int pass,
-                                                    uint32_t& count) {
+                                                    uint32_t& count, uint64_t& first_xor) {
   uint64_t first = ~0ull;
   const uint64_t w[4] = {w0, w1, w2, w3};
 #pragma unroll
   for (int j = 3; j >= 0; --j) {
-    if (w[j] != pattern_word<KIND>(pass, i + j)) { first = i + j; ++count; }
+    const uint64_t x = w[j] ^ pattern_word<KIND>(pass, i + j);
+    if (x) { first = i + j; first_xor = x; ++count; }
   }
   return first;
 }
 template <int KIND>
 __device__ __forceinline__ void compare_vec_slow(Acc& a, const u64x4& v, uint64_t g, int pass) {
   uint32_t count = 0;
-  const uint64_t first = compare_words_slow<KIND>(v.v[0], v.v[1], v.v[2], v.v[3], g << 2, pass, count);
-  if (first < a.first_idx) a.first_idx = first;
+  uint64_t fx = 0;
+  const uint64_t first = compare_words_slow<KIND>(v.v[0], v.v[1], v.v[2], v.v[3], g << 2, pass, count, fx);
+  if (first < a.first_idx) { a.first_idx = first; a.first_xor = fx; }
   a.mism += count;
 }
 
@@ -85,28 +110,33 @@ __device__ __forceinline__ void acc_vec(Acc& a, const u64x4& v, uint64_t g, int 
 }
 
 // Reduce across the CTA (finalize kernel only); the result is valid in thread 0.
+// lowest first_idx over the warp, with the xor that belongs to it
+__device__ __forceinline__ void warp_min_first(Acc& a) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) {
+    const uint64_t oi = shfl_xor_u64(a.first_idx, m);
+    const uint64_t ox = shfl_xor_u64(a.first_xor, m);
+    if (oi < a.first_idx) { a.first_idx = oi; a.first_xor = ox; }
+  }
+}
 __device__ __forceinline__ void block_reduce(Acc& a) {
-  __shared__ uint64_t sh[kThreads / 32][5];
+  __shared__ uint64_t sh[kThreads / 32][6];
   a.sum = warp_sum_u64(a.sum);
   a.xr = warp_xor_u64(a.xr);
   a.wsum = warp_sum_u64(a.wsum);
   a.mism = warp_sum_u64(a.mism);
-#pragma unroll
-  for (int m = 16; m > 0; m >>= 1) {
-    const uint64_t oi = shfl_xor_u64(a.first_idx, m);
-    if (oi < a.first_idx) a.first_idx = oi;
-  }
+  warp_min_first(a);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (lane == 0) {
     sh[warp][0] = a.sum; sh[warp][1] = a.xr; sh[warp][2] = a.wsum;
-    sh[warp][3] = a.mism; sh[warp][4] = a.first_idx;
+    sh[warp][3] = a.mism; sh[warp][4] = a.first_idx; sh[warp][5] = a.first_xor;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int w = 1; w < kThreads / 32; ++w) {
       a.sum += sh[w][0]; a.xr ^= sh[w][1]; a.wsum += sh[w][2]; a.mism += sh[w][3];
-      if (sh[w][4] < a.first_idx) a.first_idx = sh[w][4];
+      if (sh[w][4] < a.first_idx) { a.first_idx = sh[w][4]; a.first_xor = sh[w][5]; }
     }
   }
 }
@@ -180,11 +210,7 @@ pattern_verify_kernel(const uint64_t* __restrict__ words, uint64_t nvec, int pas
   const bool any_bad = __any_sync(0xffffffffu, a.mism != 0);
   if (any_bad) {  // cold
     a.mism = warp_sum_u64(a.mism);
-#pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
-      const uint64_t oi = shfl_xor_u64(a.first_idx, m);
-      if (oi < a.first_idx) a.first_idx = oi;
-    }
+    warp_min_first(a);
   }
   if ((threadIdx.x & 31) == 0) {
     VerifySlot* s = slots + ((blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5)) & (kVerifySlots - 1));
@@ -193,7 +219,7 @@ pattern_verify_kernel(const uint64_t* __restrict__ words, uint64_t nvec, int pas
     atomicAdd(reinterpret_cast<unsigned long long*>(&s->wsum), (unsigned long long)a.wsum);
     if (any_bad) {
       atomicAdd(reinterpret_cast<unsigned long long*>(&s->mismatches), (unsigned long long)a.mism);
-      atomicMin(reinterpret_cast<unsigned long long*>(&s->first_bad_index), (unsigned long long)a.first_idx);
+      first_bad_min(s, a.first_idx, a.first_xor);
     }
   }
 }
@@ -208,18 +234,15 @@ pattern_verify_finalize_kernel(const uint64_t* __restrict__ words, int pass,
   for (int b = threadIdx.x; b < kVerifySlots; b += kThreads) {
     VerifySlot* s = slots + b;
     a.sum += s->sum; a.xr ^= s->xor_; a.wsum += s->wsum; a.mism += s->mismatches;
-    if (s->first_bad_index < a.first_idx) a.first_idx = s->first_bad_index;
-    s->sum = 0; s->xor_ = 0; s->wsum = 0; s->mismatches = 0; s->first_bad_index = ~0ull;  // rest state
+    if (s->first_bad_index < a.first_idx) { a.first_idx = s->first_bad_index; a.first_xor = s->first_bad_xor; }
+    s->sum = 0; s->xor_ = 0; s->wsum = 0; s->mismatches = 0; s->first_bad_index = ~0ull; s->first_bad_xor = 0;  // rest state
   }
   block_reduce(a);
   if (threadIdx.x == 0) {
     gp_pattern_result r;
     r.sum = a.sum; r.xor_ = a.xr; r.wsum = a.wsum; r.mismatches = a.mism;
     r.first_bad_index = a.first_idx;
-    r.first_bad_xor = 0;
-    if constexpr (KIND != kPatNone) {
-      if (a.first_idx != ~0ull) r.first_bad_xor = words[a.first_idx] ^ pattern_word<KIND>(pass, a.first_idx);
-    }
+    r.first_bad_xor = a.first_idx != ~0ull ? a.first_xor : 0;  // the bits seen when the word was read, not a re-read
     *result = r;
   }
 }
@@ -227,7 +250,7 @@ pattern_verify_finalize_kernel(const uint64_t* __restrict__ words, int pass,
 __global__ void verify_scratch_init_kernel(VerifySlot* slots) {
   for (int b = threadIdx.x; b < kVerifySlots; b += blockDim.x) {
     slots[b].sum = 0; slots[b].xor_ = 0; slots[b].wsum = 0; slots[b].mismatches = 0;
-    slots[b].first_bad_index = ~0ull; slots[b].pad[0] = slots[b].pad[1] = slots[b].pad[2] = 0;
+    slots[b].first_bad_index = ~0ull; slots[b].first_bad_xor = 0; slots[b].pad[0] = slots[b].pad[1] = 0;
   }
 }
 

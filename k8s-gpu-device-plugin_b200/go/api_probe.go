@@ -17,7 +17,7 @@ import (
 // Probe : 按需重新探测 — re-grade now (all devices, or ?uuid=GPU-…), feed ListAndWatch and
 // the gauges, answer with the results.
 func (a *API) Probe(c echo.Context) error {
-	results, err := a.pluginManager.Reprobe(c.QueryParam("uuid"))
+	results, err := a.pluginManager.Reprobe(c.QueryParam("uuid"), false) // on demand: busy devices are probed too
 	if err != nil {
 		return c.JSON(http.StatusOK, util.Failed(404, err.Error()))
 	}

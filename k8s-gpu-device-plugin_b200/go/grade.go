@@ -1,6 +1,6 @@
 // NOT COMPILED in this repository (no Go toolchain in the build image).  The patch to the
 // reference's device and plugin packages; each block names the file:line it replaces or
-// extends.  host/probe.hpp is the compiled, tested C++ twin of this logic.
+// extends.  host/probe.hpp (GradeDevices, NvidiaDevicePlugin) is the compiled, tested C++ twin.
 package device
 
 import (
@@ -14,66 +14,97 @@ import (
 // goroutine while device/devices.go:159-166 (GetPluginDevices) reads it.
 var healthMu sync.RWMutex
 
+// New field on Device (device/devices.go:21-29), never serialised to kubelet:
+//	Probe *bmk.ProbeResult
+
 // GradeDevices runs after build() (device/device_map.go:34-45) and before startPlugins
 // (plugin/manager.go:71): the verdict replaces the Healthy that BuildDevice hard-codes at
-// device/devices.go:74.  Full GPUs are graded together; MIG slices ("i:j" indices,
-// device/device.go:32-34) need one child process each and are handled by the caller via
-// `gpuprobe-slice` (host/probe_slice.cpp).
-func GradeDevices(dm DeviceMap, p *bmk.Probe, mask uint32) (unhealthy int) {
+// device/devices.go:74.  Full GPUs are graded in this process, one goroutine each; every MIG
+// slice ("i:j" index, device/device.go:32-34) is graded by one gpuprobe-slice child process,
+// sized to the slice's TotalMemory.  A device whose probe errors — a slice with no slice binary
+// configured included — is Unhealthy, never silently Healthy.  applyHealth is true at start-up
+// (nothing is advertised yet); false for a re-probe, where ListAndWatch owns the transition.
+func GradeDevices(dm DeviceMap, p *bmk.Probe, mask uint32, applyHealth bool) (unhealthy int) {
+	type job struct {
+		d   *Device
+		mig bool
+	}
 	seen := map[string]bool{}
-	var uuids []string
+	var jobs []job
 	for _, devs := range dm {
 		for _, d := range devs {
-			if d.IsMigDevice() || seen[d.GetUUID()] {
+			if seen[d.GetUUID()] {
 				continue
 			}
 			seen[d.GetUUID()] = true
-			uuids = append(uuids, d.GetUUID())
+			jobs = append(jobs, job{d, d.IsMigDevice()})
 		}
 	}
-	verdict := map[string]bool{}
+	verdict := map[string]*bmk.ProbeResult{}
 	var wg sync.WaitGroup
 	var mu sync.Mutex
-	for _, u := range uuids {
+	for _, j := range jobs {
 		wg.Add(1)
-		go func(u string) {
+		go func(j job) {
 			defer wg.Done()
-			res, err := p.ProbeDevice(u, mask)
+			var res bmk.ProbeResult
+			var err error
+			if j.mig {
+				res, err = p.ProbeChild(j.d.GetUUID(), mask, j.d.TotalMemory)
+			} else {
+				res, err = p.ProbeDevice(j.d.GetUUID(), mask)
+			}
+			if err != nil || res.Error != 0 {
+				res.Healthy = false
+			}
 			mu.Lock()
-			verdict[u] = err == nil && res.Healthy
+			verdict[j.d.GetUUID()] = &res
 			mu.Unlock()
-		}(u)
+		}(j)
 	}
 	wg.Wait()
 	healthMu.Lock()
 	defer healthMu.Unlock()
 	for _, devs := range dm {
-		for _, d := range devs {
-			ok, graded := verdict[d.GetUUID()]
+		for _, d := range devs { // replicas (uuid::n) share their GPU's verdict
+			res, graded := verdict[d.GetUUID()]
 			if !graded {
 				continue
 			}
-			if ok {
-				d.Health = pluginapi.Healthy
-			} else {
-				d.Health = pluginapi.Unhealthy // a probe that errored is never silently Healthy
+			d.Probe = res
+			if !res.Healthy {
 				unhealthy++
+			}
+			if applyHealth {
+				if res.Healthy {
+					d.Health = pluginapi.Healthy
+				} else {
+					d.Health = pluginapi.Unhealthy
+				}
 			}
 		}
 	}
 	return unhealthy
 }
 
-// HealthEvent is what the probe ticker / GET /probe sends on plugin.health.  The reference's
-// channel carries *Device and can only mark Unhealthy (plugin/plugin.go:181-186); the patched
-// ListAndWatch arm is:
+// HealthEvent is what the probe ticker / GET /probe delivers to ListAndWatch.  The reference's
+// channel is `chan *device.Device`, unbuffered, and can only mark Unhealthy
+// (plugin/plugin.go:40,53,181-186).  The patch:
 //
-//	case ev := <-plugin.health:
-//	    healthMu.Lock()
-//	    changed := ev.Device.Health != ev.Health()
-//	    ev.Device.Health = ev.Health()
-//	    healthMu.Unlock()
-//	    if changed { s.Send(&pluginapi.ListAndWatchResponse{Devices: plugin.Devices().GetPluginDevices()}) }
+//	plugin/plugin.go:40   health chan device.HealthEvent
+//	plugin/plugin.go:53   health: make(chan device.HealthEvent, 4*len(devices)+16),   // buffered
+//	plugin/plugin.go:181  case ev := <-plugin.health:
+//	                          healthMu.Lock()
+//	                          changed := ev.Device.Health != ev.Health()
+//	                          ev.Device.Health = ev.Health()
+//	                          healthMu.Unlock()
+//	                          if changed {
+//	                              s.Send(&pluginapi.ListAndWatchResponse{Devices: plugin.Devices().GetPluginDevices()})
+//	                          }
+//
+// and the writer never blocks (Report below): with no ListAndWatch stream open — kubelet not yet
+// connected, or between reconnects — an unbuffered send would park the probe ticker and
+// GET /probe for ever.  The C++ twin uses an unbounded queue (NvidiaDevicePlugin::Report).
 type HealthEvent struct {
 	Device  *Device
 	Healthy bool
@@ -84,4 +115,17 @@ func (e HealthEvent) Health() string {
 		return pluginapi.Healthy
 	}
 	return pluginapi.Unhealthy
+}
+
+// Report delivers ev without ever blocking.  If the buffer is full (nobody has been listening for
+// a long time) the verdict is applied to the device directly, so the first list of the next
+// ListAndWatch stream (plugin/plugin.go:174) already carries it.
+func Report(ch chan HealthEvent, ev HealthEvent) {
+	select {
+	case ch <- ev:
+	default:
+		healthMu.Lock()
+		ev.Device.Health = ev.Health()
+		healthMu.Unlock()
+	}
 }

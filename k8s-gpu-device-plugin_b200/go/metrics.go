@@ -5,6 +5,8 @@
 package metrics
 
 import (
+	"strconv"
+
 	bmk "github.com/uppercaveman/k8s-gpu-device-plugin/benchmark"
 
 	"github.com/prometheus/client_golang/prometheus"
@@ -29,6 +31,38 @@ var (
 	GemmTFlops = gauge("gpu_probe_gemm_tflops", "bf16 GEMM throughput on tcgen05, median")
 	GemmErr    = gauge("gpu_probe_gemm_max_scaled_err", "max |c-ref| / sum|a||b| over the sampled entries")
 )
+
+var (
+	P2PGBps      = prometheus.NewGaugeVec(prometheus.GaugeOpts{Name: "gpu_probe_p2p_gbps", Help: "NVLink peer bandwidth measured with in-kernel loads/stores"}, []string{"src", "dst", "dir"})
+	AllreduceBus = prometheus.NewGaugeVec(prometheus.GaugeOpts{Name: "gpu_probe_allreduce_busbw_gbps", Help: "ncclAllReduce bus bandwidth"}, []string{"ranks"})
+	FabricOK     = prometheus.NewGaugeVec(prometheus.GaugeOpts{Name: "gpu_probe_fabric_healthy", Help: "1 if the P2P matrix and the all-reduce met their floors and every transfer carried the right bytes"}, []string{"gpus"})
+	FabricSpread = prometheus.NewGaugeVec(prometheus.GaugeOpts{Name: "gpu_probe_fabric_spread", Help: "max/min over the off-diagonal P2P pairs (1.0 = flat)"}, []string{"gpus"})
+)
+
+func init() { prometheus.MustRegister(P2PGBps, AllreduceBus, FabricOK, FabricSpread) }
+
+// UpdateFabric is called once per loadPlugins, after gp_probe_fabric.  Twin: PluginManager::GradeFabric.
+func UpdateFabric(f bmk.FabricResult) {
+	n := strconv.Itoa(f.N)
+	for i := 0; i < f.N; i++ {
+		for j := 0; j < f.N; j++ {
+			if i == j {
+				continue
+			}
+			P2PGBps.WithLabelValues(strconv.Itoa(i), strconv.Itoa(j), "read").Set(f.Read[i*f.N+j])
+			P2PGBps.WithLabelValues(strconv.Itoa(i), strconv.Itoa(j), "write").Set(f.Write[i*f.N+j])
+		}
+	}
+	if f.AllreduceError == 0 {
+		AllreduceBus.WithLabelValues(n).Set(f.AllreduceBusbwGBps)
+	}
+	ok := 0.0
+	if f.Healthy {
+		ok = 1
+	}
+	FabricOK.WithLabelValues(n).Set(ok)
+	FabricSpread.WithLabelValues(n).Set(f.Spread)
+}
 
 // Update is called after every probe: start-up grade, periodic tick, GET /probe.
 func Update(index string, r bmk.ProbeResult) {

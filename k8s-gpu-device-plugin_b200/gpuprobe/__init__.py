@@ -108,6 +108,7 @@ class DeviceResult(C.Structure):
         ("pattern_digest", C.c_uint64), ("gemm", GemmResult),
         ("alloc_s", C.c_double), ("free_s", C.c_double), ("kernels_s", C.c_double),
         ("arena_bytes", C.c_uint64), ("arena_reused", C.c_uint32), ("arena_backend", C.c_uint32),
+        ("free_deferred", C.c_uint32), ("reserved3", C.c_uint32),
     ]
 
 

@@ -5,6 +5,10 @@
 // directly.  Used by tests/test_host_gpu.py.
 //   plugin_sim [--hbm-mib N] [--pattern-mib N] [--wo N] [--gemm N] [--mask M] [--slice BIN] [--min-copy G]
 //              [--scenario manager] [--fabric-mib N] [--min-p2p G]
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
+
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -40,9 +44,18 @@ static std::string listJson(const std::vector<PluginDevice>& l) {
 // --scenario manager: the PluginManager path on real GPUs — loadPlugins grades every GPU and then the fabric
 // (P2P matrix + all-reduce) in one go, the matrix feeds the gauges and GetPreferredAllocation; then the
 // isolation path: a child that faults, a child that never answers (killed at the deadline), and the way back.
-static int manager_scenario(gp_config cfg, uint32_t mask, const std::string& slice_bin) {
+// --assume-idle 1: the harness that starts this binary (pytest, with its own CUDA context on GPU 0) is itself a
+// "tenant" in NVML's eyes; a test that wants every GPU graded tells the backend to treat them as idle
+struct AssumeIdleBackend : GpuProbeBackend {
+  using GpuProbeBackend::GpuProbeBackend;
+  bool assume_idle = false;
+  int OtherComputeProcs(const std::string& u) override { return assume_idle ? 0 : GpuProbeBackend::OtherComputeProcs(u); }
+};
+
+static int manager_scenario(gp_config cfg, uint32_t mask, const std::string& slice_bin, bool assume_idle) {
   cfg.keep_arena = 1;
-  GpuProbeBackend be(&cfg, slice_bin);
+  AssumeIdleBackend be(&cfg, slice_bin);
+  be.assume_idle = assume_idle;
   if (be.init_rc()) { printf("{\"error\":\"gp_init: %s\"}\n", be.init_error().c_str()); return 1; }
   const int n = gp_device_count(be.ctx());
   std::vector<std::shared_ptr<CudaDeviceInfo>> infos;
@@ -109,11 +122,23 @@ static int manager_scenario(gp_config cfg, uint32_t mask, const std::string& sli
   printf("],\"log\":[");
   auto log = mgr.log();
   for (size_t i = 0; i < log.size(); ++i) printf("%s\"%s\"", i ? "," : "", jsonEscape(log[i]).c_str());
-  printf("],\"metrics\":\"%s\"}\n", jsonEscape(metrics.Render()).c_str());
+  printf("],\"busy_skipped\":%d,\"metrics\":\"%s\"}\n", mgr.skippedBusy(), jsonEscape(metrics.Render()).c_str());
+  fflush(stdout);
   return rc;
 }
 
+// a crash in the harness must say where: print the stack and leave (no core files on the GPU boxes)
+static void on_fatal_signal(int sig) {
+  void* frames[48];
+  const int n = backtrace(frames, 48);
+  dprintf(STDERR_FILENO, "plugin_sim: fatal signal %d, stack:\n", sig);
+  backtrace_symbols_fd(frames, n, STDERR_FILENO);
+  _exit(128 + sig);
+}
+
 int main(int argc, char** argv) {
+  signal(SIGSEGV, on_fatal_signal);
+  signal(SIGABRT, on_fatal_signal);
   gp_config cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.struct_size = sizeof(cfg);
@@ -126,6 +151,7 @@ int main(int argc, char** argv) {
   cfg.warmup = 1;
   uint32_t mask = GP_PROBE_ALL_SINGLE;
   std::string slice_bin, scenario;
+  bool assume_idle = false;
   for (int i = 1; i + 1 < argc; i += 2) {
     const std::string a = argv[i];
     const char* v = argv[i + 1];
@@ -139,8 +165,9 @@ int main(int argc, char** argv) {
     else if (a == "--scenario") scenario = v;
     else if (a == "--fabric-mib") cfg.fabric_bytes = strtoull(v, nullptr, 10) << 20;
     else if (a == "--min-p2p") cfg.min_p2p_gbps = atof(v);
+    else if (a == "--assume-idle") assume_idle = atoi(v) != 0;
   }
-  if (scenario == "manager") return manager_scenario(cfg, mask, slice_bin);
+  if (scenario == "manager") return manager_scenario(cfg, mask, slice_bin, assume_idle);
   GpuProbeBackend be(&cfg, slice_bin);
   if (be.init_rc()) {
     printf("{\"error\":\"gp_init: %s\"}\n", be.init_error().c_str());

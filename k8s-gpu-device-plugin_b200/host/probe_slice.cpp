@@ -3,7 +3,7 @@
 // CUDA_VISIBLE_DEVICES=MIG-<uuid> before exec: a CUDA process sees a single MIG compute
 // instance at a time, so per-slice probing (device/device_map.go:78-98 visits each slice,
 // device/device.go:32-34 names them "i:j") needs a process per slice, not a thread.
-//   argv: mask hbm_bytes pattern_bytes wo_passes gemm_mnk iters warmup [--test-hang] [--test-cuda-error N]
+//   argv: mask hbm_bytes pattern_bytes wo_passes gemm_mnk iters warmup [--test-hang] [--test-cuda-error N] [--sm-limit N]
 // The two --test-* switches exist for the parent's own tests: a child that never answers, and a child whose
 // device reports a sticky CUDA fault (injected at the API level, nothing abnormal reaches the GPU).
 #include <unistd.h>
@@ -29,6 +29,7 @@ int main(int argc, char** argv) {
   for (int i = 8; i < argc; ++i) {
     if (!strcmp(argv[i], "--test-hang")) { for (;;) pause(); }
     if (!strcmp(argv[i], "--test-cuda-error") && i + 1 < argc) test_cuda_error = atoi(argv[++i]);
+    if (!strcmp(argv[i], "--sm-limit") && i + 1 < argc) cfg.sm_limit = (uint32_t)atoi(argv[++i]);  // size grids as a slice would
   }
   gp_device_result out;
   memset(&out, 0, sizeof(out));

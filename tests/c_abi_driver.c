@@ -42,7 +42,7 @@ int main(void) {
   if (gp_device_count(ctx) < 1 || gp_device_uuid(ctx, 0, uuid, sizeof(uuid)) != GP_OK) return 21;
   rc = gp_probe_device(ctx, uuid, GP_PROBE_COPY | GP_PROBE_TRIAD | GP_PROBE_PATTERN, &res);
   if (rc != GP_OK || !res.healthy || res.struct_size != sizeof(res)) return 22;
-  if (res.kernels_s <= 0 || res.alloc_s < 0 || res.free_s < 0 || res.arena_bytes == 0) return 27;
+  if (res.kernels_s <= 0 || res.alloc_s <= 0 || res.free_s != 0 || res.arena_bytes == 0 || res.free_deferred != 1) return 27;
   if (gp_pattern_fill(ctx, uuid, GP_PAT_ADDRESS, 1, 4096) != GP_OK) return 23;
   if (gp_inject_bitflip(ctx, uuid, 77, 9) != GP_OK) return 24;
   if (gp_pattern_verify(ctx, uuid, GP_PAT_ADDRESS, 1, 4096, &pr) != GP_OK) return 25;

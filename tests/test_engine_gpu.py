@@ -87,6 +87,10 @@ def test_nvml_snapshot():
         assert 100 < i.sm_clock_max_mhz < 4000 and i.sm_clock_mhz <= i.sm_clock_max_mhz
         assert i.mem_total_bytes > (100 << 30) and i.power_mw > 1000 and 0 < i.temperature_c < 110
         assert i.other_compute_procs == 0  # a fresh box: nobody else is computing here
+        # ... and still nobody once THIS process holds a context on the device: NVML lists host pids, which
+        # getpid() does not match inside a container, and the library must not count itself as a tenant
+        p.pattern_fill(p.device_uuid(0), 0, 0, 64)
+        assert p.nvml_snapshot(p.device_uuid(0)).other_compute_procs == 0
         with pytest.raises(gpuprobe.GpuProbeError):
             p.nvml_snapshot("GPU-00000000-0000-0000-0000-000000000000")
 
@@ -100,23 +104,35 @@ def test_whole_memory_grading():
         assert r.verify_gbps_best > 1000 and r.fill_gbps_best > 1000
 
 
-@pytest.mark.parametrize("backend", [gpuprobe.GP_ARENA_VMM, gpuprobe.GP_ARENA_MALLOC], ids=["vmm", "cudaMalloc"])
+@pytest.mark.parametrize("backend", [gpuprobe.GP_ARENA_VMM, gpuprobe.GP_ARENA_MALLOC, gpuprobe.GP_ARENA_AUTO],
+                         ids=["vmm", "cudaMalloc", "auto"])
 def test_arena_time_is_reported_and_a_kept_arena_costs_nothing(backend):
-    """gp_device_result says where the call's time went.  keep_arena = 0: every call grows and releases the
-    arena (alloc_s, free_s > 0).  keep_arena = 1 (the periodic re-probe of an idle device): the second call
-    finds the arena in place — no allocation inside the call — until gp_trim_device hands it back."""
+    """gp_device_result says where the call's time went.  keep_arena = 0: every call grows the arena
+    (alloc_s > 0) and hands it to the reaper thread on return (free_deferred, free_s = 0); the next call
+    waits for that release before it allocates.  keep_arena = 1 (the periodic re-probe of an idle device): the
+    second call finds the arena in place — no allocation inside the call — until gp_trim_device hands it back."""
     mask = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_PATTERN
     kw = dict(hbm_bytes=1 << 30, wo_passes=2, iters=2, warmup=1, arena_backend=backend)
+    used = {gpuprobe.GP_ARENA_AUTO: gpuprobe.GP_ARENA_MALLOC}.get(backend, backend)  # AUTO, cold every call: cudaMalloc
     with gpuprobe.Probe(keep_arena=0, **kw) as p:
         for _ in range(2):
             r = p.probe_device("0", mask)
-            assert r.healthy == 1 and r.arena_backend == backend and r.arena_reused == 0
-            assert r.alloc_s > 0 and r.free_s > 0 and r.arena_bytes >= 2 << 30
+            assert r.healthy == 1 and r.arena_backend == used and r.arena_reused == 0
+            assert r.alloc_s > 0 and r.free_s == 0 and r.free_deferred == 1 and r.arena_bytes >= 2 << 30
             assert abs(r.duration_s - (r.alloc_s + r.free_s + r.kernels_s)) < 1e-9
+        # all four probes cold: the GEMM runs in its own small buffer while the arena is allocated behind it
+        r = p.probe_device("0", gpuprobe.GP_PROBE_ALL_SINGLE)
+        assert r.healthy == 1 and r.probed_mask == gpuprobe.GP_PROBE_ALL_SINGLE and r.gemm.samples_bad == 0
+        p.trim()   # joins the reaper: the memory is back
+        import torch
+        free, total = torch.cuda.mem_get_info(0)
+        assert free > total - (24 << 30)   # nothing of ours is left (the session fixtures keep a few GiB)
+    used = {gpuprobe.GP_ARENA_AUTO: gpuprobe.GP_ARENA_VMM}.get(backend, backend)     # AUTO, kept arena: VMM
     with gpuprobe.Probe(keep_arena=1, **kw) as p:
         first = p.probe_device("0", mask)
         again = p.probe_device("0", mask)
-        assert first.alloc_s > 0 and first.arena_reused == 0 and first.free_s == 0
+        assert first.alloc_s > 0 and first.arena_reused == 0 and first.free_s == 0 and first.arena_backend == used
+        assert again.free_deferred == 0
         assert again.alloc_s == 0 and again.free_s == 0 and again.arena_reused == 1 and again.healthy == 1
         # growing a kept arena maps only the difference and leaves the lower part where it was
         p.pattern_fill("0", gpuprobe.GP_PAT_ADDRESS, 0, (1 << 30) // 8)

@@ -15,7 +15,10 @@ HOST = os.path.join(ROOT, "k8s-gpu-device-plugin_b200", "host")
 def run_sim(*args):
     r = subprocess.run([os.path.join(HOST, "plugin_sim"), *args], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
-    return json.loads(r.stdout)
+    # NCCL prints its version banner on stdout when NCCL_DEBUG is set in the environment: take the JSON line
+    doc = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(doc) == 1, r.stdout[:2000]
+    return json.loads(doc[0])
 
 
 def test_plugin_sim_healthy_path():
@@ -52,8 +55,11 @@ def test_manager_scenario_fabric_and_isolation():
     """PluginManager on real GPUs: grade + fabric inside loadPlugins, then the isolated re-probe path: a child
     whose device reports a sticky fault, a child that never answers (killed at the deadline), and the way back
     to Healthy each time, with the plugin's own process and context untouched."""
-    d = run_sim("--scenario", "manager", "--slice", os.path.join(HOST, "gpuprobe-slice"), "--fabric-mib", "64")
-    assert d["devices"] >= 1 and d["unhealthy"] == 0
+    # --assume-idle: this pytest process holds a CUDA context on GPU 0, which NVML rightly reports as a tenant
+    d = run_sim("--scenario", "manager", "--slice", os.path.join(HOST, "gpuprobe-slice"), "--fabric-mib", "64",
+                "--assume-idle", "1")
+    assert d["devices"] >= 1 and d["unhealthy"] == 0 and d["busy_skipped"] == 0
+    assert "gpu_probe_hbm_copy_gbps" in d["metrics"]   # the devices really were graded at load (not skipped as busy)
     steps = {s["step"]: s for s in d["steps"]}
     assert steps["isolated"]["verdict"] == "Healthy" and steps["isolated"]["error"] == 0
     assert steps["child_fault"]["verdict"] == "Unhealthy" and steps["child_fault"]["error"] == -9   # GP_ERR_DEVICE_LOST
@@ -74,3 +80,44 @@ def test_manager_scenario_fabric_and_isolation():
         assert len(d["preferred"]) == 2
         assert 'gpu_probe_p2p_gbps{dir=\"read\",dst=\"1\",src=\"0\"}' in d["metrics"] or "gpu_probe_p2p_gbps{dir=\"read\"" in d["metrics"]
         assert "gpu_probe_fabric_healthy" in d["metrics"]
+
+
+def test_slice_binary_at_1g_slice_scale():
+    """No MIG on this pool, so the child is run exactly as ProbeSlice would run it for a 1g.23gb slice of a
+    B200 — arrays of SliceBytes(16 GiB, 23 GiB) = a quarter of the slice, grids sized for the slice's 18 SMs —
+    on the whole GPU addressed by its own UUID (CUDA_VISIBLE_DEVICES takes it exactly as it takes a MIG-
+    UUID).  What this covers: the sizing logic, the launchers at slice scale, the verdict and the POD
+    result over the pipe.  What it cannot: a real compute instance (DESIGN.md says so)."""
+    import ctypes
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "k8s-gpu-device-plugin_b200"))
+    import gpuprobe
+    with gpuprobe.Probe() as p:
+        uuid = p.device_uuid(0)
+    slice_mem = 23 << 30
+    hbm = min(16 << 30, slice_mem // 4) & ~((1 << 20) - 1)          # GpuProbeBackend::SliceBytes
+    assert hbm == 6174015488 & ~((1 << 20) - 1)
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES=uuid)
+    r = subprocess.run([os.path.join(HOST, "gpuprobe-slice"), "15", str(hbm), str(hbm), "4", "2048", "3", "1",
+                        "--sm-limit", "18"], capture_output=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert len(r.stdout) == ctypes.sizeof(gpuprobe.DeviceResult)
+    res = gpuprobe.DeviceResult.from_buffer_copy(r.stdout)
+    assert res.struct_size == ctypes.sizeof(gpuprobe.DeviceResult) and res.healthy == 1 and res.error == 0
+    assert res.probed_mask == gpuprobe.GP_PROBE_ALL_SINGLE and res.sm_count == 18
+    assert res.hbm_bytes == hbm and res.pattern_bytes == hbm and res.pattern_passes == 6
+    assert res.arena_bytes <= 3 * hbm + (1 << 30) < slice_mem                    # fits the slice with room to spare
+    assert res.gemm.samples_bad == 0 and 1 < res.gemm.tflops_best < 400          # 9 CTA pairs, not 74
+    assert res.copy_gbps_median > 1000 and res.verify_gbps_median > 1000
+
+
+def test_manager_leaves_a_gpu_with_a_tenant_alone():
+    """The same start-up path WITHOUT --assume-idle: this pytest process holds a CUDA context on GPU 0, so NVML
+    reports a tenant there.  loadPlugins must not give that GPU the full probe (it keeps Healthy, ungraded) and
+    must not run the fabric probe, which would drive every GPU at once."""
+    import torch
+    torch.zeros(1, device="cuda:0")   # make sure the tenant exists
+    d = run_sim("--scenario", "manager", "--fabric-mib", "64")
+    assert d["devices"] >= 1 and d["unhealthy"] == 0 and d["busy_skipped"] >= 1
+    assert d["fabric"]["ngpus"] == 0
+    assert all(x["health"] == "Healthy" for x in d["lists"][0])
