@@ -36,8 +36,15 @@ $(LIB): $(OBJS)
 oracle:
 	$(MAKE) -C oracle
 
+# development build for tools/: the launch-shape / raster / cache-hint switches become environment variables
+# (GPUPROBE_GEMM_GROUP_M, GPUPROBE_GEMM_HINTS, GPUPROBE_P2P_SHAPE).  The release library reads none of them.
+DEVLIB := $(PKG)/libgpuprobe_dev.so
+dev: $(DEVLIB)
+$(DEVLIB): $(SRCS) $(HDRS)
+	$(NVCC) $(NVFLAGS) -DGPUPROBE_DEV_SWITCHES -shared -o $@ $(SRCS) -cudart static -lpthread -ldl 2> $(CSRC)/dev.ptxas.log || (cat $(CSRC)/dev.ptxas.log; exit 1)
+
 clean:
-	rm -f $(OBJS) $(CSRC)/*.ptxas.log $(LIB) $(HOST)/host_selftest $(HOST)/gpuprobe-slice $(HOST)/plugin_sim
+	rm -f $(OBJS) $(CSRC)/*.ptxas.log $(LIB) $(DEVLIB) $(HOST)/host_selftest $(HOST)/gpuprobe-slice $(HOST)/plugin_sim
 	$(MAKE) -C oracle clean
 
-.PHONY: all oracle host clean
+.PHONY: all oracle host clean dev

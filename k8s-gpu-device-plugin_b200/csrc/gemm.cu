@@ -92,8 +92,16 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t rank
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
   return r;
 }
+// RELAXED on purpose.  The default (.release) makes the arrive wait for every earlier global store of the thread
+// to be performed (SASS: MEMBAR.ALL.GPU + ERRBAR before the arrive): the epilogue would hold the accumulator
+// until its C stores had reached memory, microseconds after the tensor memory was actually free.  What the MMA
+// thread needs ordered before it overwrites the accumulator are the tcgen05.ld reads, and those are ordered by
+// tcgen05.wait::ld + tcgen05.fence::before_thread_sync, not by this arrive.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cta_relaxed(uint32_t addr) {
+  asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const void* p) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(p) : "memory");
@@ -408,6 +416,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(b * kTileN + set * 128);
         const size_t col0 = (size_t)tn * Cfg::kTileNAll + (size_t)(h * kTileN + set * 128);
+        // release the half as soon as its last chunk is in registers; the stores that follow no longer hold it
+        auto release_half = [&] {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if constexpr (CG == 2) mbar_arrive_cluster(tempty_leader + 8u * b);
+            else mbar_arrive_cta_relaxed(tempty_bar(b));
+          }
+        };
         if constexpr (OUT == 0) {
           float* crow = reinterpret_cast<float*>(Cv) + (size_t)row * N + col0;
           float v[2][32];
@@ -416,6 +433,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           for (int c = 0; c < 4; ++c) {
             tmem_ld_wait();
             if (c + 1 < 4) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
+            else release_half();
 #pragma unroll
             for (int q = 0; q < 4; ++q) st_f8_hint(crow + c * 32 + q * 8, v[c & 1] + 8 * q, pol_c);
           }
@@ -430,6 +448,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             if (c + 1 < 2) {
               tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 64), v[(c + 1) & 1]);
               tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 64 + 32), v[(c + 1) & 1] + 32);
+            } else {
+              release_half();
             }
             uint32_t w[32];
 #pragma unroll
@@ -438,12 +458,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
             for (int q = 0; q < 4; ++q) st_u8_hint(crow + c * 64 + q * 16, w + 8 * q, pol_c);
           }
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          if constexpr (CG == 2) mbar_arrive_cluster(tempty_leader + 8u * b);
-          else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty_bar(b)) : "memory");
         }
       }
       if constexpr (NT == 2) { acc_phase ^= 1; }

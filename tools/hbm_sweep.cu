@@ -306,6 +306,35 @@ __global__ void copy_tma_np(const uint8_t* src, uint8_t* dst) {
   bulk_commit();
   bulk_wait_read<0>();
 }
+// ---- round 2 experiments: can the 1R:1W mix be un-mixed? ----------------------------------
+// (a) copy_tma_np with an L2 prefetch of the chunk that the CTA `DIST` places ahead will load
+__device__ __forceinline__ void bulk_prefetch_l2(const void* g, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(g), "r"(bytes) : "memory");
+}
+template <int TILE, int NT, int DIST>
+__global__ void copy_tma_np_pf(const uint8_t* src, uint8_t* dst, uint64_t total) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t full[NT];
+  if (threadIdx.x != 0) return;
+  for (int t = 0; t < NT; ++t) mbar_init(&full[t], 1);
+  mbar_fence_init();
+  const uint64_t span = (uint64_t)TILE * NT;
+  const uint64_t base = (uint64_t)blockIdx.x * span;
+  const uint64_t ahead = base + (uint64_t)DIST * span;
+  if (ahead + span <= total)
+    for (int t = 0; t < NT; ++t) bulk_prefetch_l2(src + ahead + (uint64_t)t * TILE, TILE);
+  for (int t = 0; t < NT; ++t) { mbar_expect_tx(&full[t], TILE); bulk_g2s(smem + t * TILE, src + base + (uint64_t)t * TILE, TILE, &full[t]); }
+  for (int t = 0; t < NT; ++t) { mbar_wait(&full[t], 0); bulk_s2g(dst + base + (uint64_t)t * TILE, smem + t * TILE, TILE); }
+  bulk_commit();
+  bulk_wait_read<0>();
+}
+// (b) phase separation at L2-window grain: one tiny kernel pulls window w+1 of the source into L2 (reads only),
+// the next kernel copies window w (its loads hit L2, DRAM sees writes only)
+__global__ void l2_pull_window(const uint8_t* src, uint64_t bytes) {
+  const uint64_t off = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16384ull;
+  if (off < bytes) bulk_prefetch_l2(src + off, 16384);
+}
+
 template <int U>
 __global__ void triad_np(float* a, const float* b, const float* c, float s) {
   const uint64_t g0 = ((uint64_t)blockIdx.x * blockDim.x * U + threadIdx.x) * 8;
@@ -409,6 +438,16 @@ int main(int argc, char** argv) {
 
 #define COPY_TMA_NP(TILE, NT) { CK(cudaFuncSetAttribute(copy_tma_np<TILE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE * NT)); cases.push_back({"copy_tma_np tile" #TILE " nt" #NT, 2.0 * N, [=](cudaStream_t st) { copy_tma_np<TILE, NT><<<(unsigned)(N / (TILE * NT)), 32, TILE * NT, st>>>(a, b); }}); }
   COPY_TMA_NP(16384, 1); COPY_TMA_NP(16384, 2); COPY_TMA_NP(16384, 4); COPY_TMA_NP(32768, 1); COPY_TMA_NP(32768, 2); COPY_TMA_NP(8192, 1); COPY_TMA_NP(8192, 2); COPY_TMA_NP(8192, 4); COPY_TMA_NP(65536, 1); COPY_TMA_NP(4096, 4); COPY_TMA_NP(4096, 1); COPY_TMA_NP(24576, 1);
+#define COPY_TMA_NP_PF(TILE, NT, DIST) { CK(cudaFuncSetAttribute(copy_tma_np_pf<TILE, NT, DIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, TILE * NT)); cases.push_back({"r2 copy_tma_np+prefetchL2 tile" #TILE " nt" #NT " dist" #DIST, 2.0 * N, [=](cudaStream_t st) { copy_tma_np_pf<TILE, NT, DIST><<<(unsigned)(N / (TILE * NT)), 32, TILE * NT, st>>>(a, b, N); }}); }
+  COPY_TMA_NP(16384, 4);  // the shipped shape, as the baseline of this block
+  COPY_TMA_NP_PF(16384, 4, 148); COPY_TMA_NP_PF(16384, 4, 512); COPY_TMA_NP_PF(16384, 4, 1024); COPY_TMA_NP_PF(16384, 4, 4096); COPY_TMA_NP_PF(16384, 4, 64);
+#define COPY_WINDOWED(WMIB) cases.push_back({"r2 copy windowed: pull " #WMIB " MiB into L2, then copy it", 2.0 * N, [=](cudaStream_t st) { \
+    const uint64_t W = (uint64_t)WMIB << 20; \
+    l2_pull_window<<<(unsigned)(W / 16384 / 64), 64, 0, st>>>(a, W); \
+    for (uint64_t off = 0; off + W <= N; off += W) { /* W must divide N: a partial window is skipped, never overrun */ \
+      if (off + 2 * W <= N) l2_pull_window<<<(unsigned)(W / 16384 / 64), 64, 0, st>>>(a + off + W, W); \
+      copy_tma_np<16384, 4><<<(unsigned)(W / 65536), 32, 65536, st>>>(a + off, b + off); } }})
+  COPY_WINDOWED(32); COPY_WINDOWED(64);  // (96 MiB does not divide the array; 128 MiB no longer fits L2)
   { const uint64_t NT3 = N / 2; float* fa = (float*)a; float* fb = (float*)b; float* fc = (float*)(b + NT3);
 #define TRIAD_NP(U, T) cases.push_back({"triad_np U" #U " t" #T, 3.0 * NT3, [=](cudaStream_t st) { triad_np<U><<<(unsigned)(NT3 / 32 / (T * U)), T, 0, st>>>(fa, fb, fc, 3.0f); }})
     TRIAD_NP(1, 256); TRIAD_NP(2, 256); TRIAD_NP(4, 256); TRIAD_NP(2, 512); TRIAD_NP(1, 512); TRIAD_NP(2, 128); TRIAD_NP(1, 1024);
@@ -424,6 +463,7 @@ int main(int argc, char** argv) {
     if (*filter && c.name.find(filter) == std::string::npos) continue;
     for (int i = 0; i < 2; ++i) c.run(s);
     CK(cudaStreamSynchronize(s));
+    CK(cudaGetLastError());
     const int iters = 7;
     for (int i = 0; i < iters; ++i) { CK(cudaEventRecord(ev[i], s)); c.run(s); }
     CK(cudaEventRecord(ev[iters], s));
