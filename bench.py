@@ -16,6 +16,15 @@ Multi-GPU (torchrun, one rank per GPU): the path shards as independent devices, 
 ranks run the same per-GPU workload with no data-path collective ("scaling": "weak");
 torch.distributed (NCCL) is used only for the barrier and the max-over-ranks time.
 
+Beside `value` the line carries: `e2e` (gp_probe_device through the C ABI, the periodic
+re-probe of an idle device with its arena kept) and `e2e_cold` (the same call allocating and
+releasing every time, with alloc/free/kernel seconds); `sweep` (gp_probe_all over all N GPUs
+from rank 0: the second half of the metric); `gemm` (configs[2]); and at N >= 2, from rank 0
+with the other ranks parked on a host barrier, the only cross-GPU paths (configs[4]): `p2p`
+(in-kernel read / write / bidirectional matrices at 1 GiB with every transfer's data checked,
+the cudaMemcpyPeerAsync yardstick in the same schedule, the all-at-once round and the 64 KiB -
+1 GiB ladder), `allreduce` (NCCL bus bandwidth over the ladder + 4 GiB) and `fabric` (the verdict).
+
 The reference (uppercaveman/k8s-gpu-device-plugin) has no implementation of this path
 (benchmark/benchmark.go is a pprof wrapper) and no Go toolchain exists here, so the
 `--impl reference` arm and `cpu_baseline` time this repo's CPU port of the frozen spec
@@ -435,8 +444,9 @@ def run_ours(args):
         # free_s say what the allocator costs when all N processes hit the driver at once
         p2 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
         p2.probe_device(dev, mask)
-        e2e_cold = e2e_leg(p2, e2e_calls, "same call with keep_arena = 0: the arena is mapped at entry and "
-                                          "released before return on every call")
+        e2e_cold = e2e_leg(p2, e2e_calls, "same call with keep_arena = 0, back to back: cudaMalloc at entry, the arena "
+                                          "handed to a release thread at return; each call first waits for its "
+                                          "predecessor's release (alloc_s_per_call is that wait plus the allocation)")
 
     # ---- the literal host-buffer reading of e2e, for the record: grade 1 GiB that lives in pinned HOST
     # memory (H2D copy + verify + 48-byte result back).  This measures PCIe, not the device, and is not
@@ -475,10 +485,21 @@ def run_ours(args):
         host_barrier()
         if rank == 0:
             p3 = gpuprobe.Probe(keep_arena=0, hbm_bytes=nbytes, stream_variant=variant)
+            def timed_sweep(mask):
+                # first call of the process on these GPUs (context creation, module load), then the memory of that
+                # call is allowed to arrive back at the driver (gp_trim joins the release threads) before the
+                # timed call starts: a cold-arena sweep as the plugin runs it, not one queued behind its predecessor
+                res, first = p3.probe_all(n_gpus, mask)
+                p3.trim()
+                res, wall = p3.probe_all(n_gpus, mask)
+                t0 = time.perf_counter()
+                p3.trim()
+                return res, first, wall, time.perf_counter() - t0
             try:
-                res, wall_cold = p3.probe_all(n_gpus, gpuprobe.GP_PROBE_ALL_SINGLE)
-                res, wall_warm = p3.probe_all(n_gpus, gpuprobe.GP_PROBE_ALL_SINGLE)
-                sweep = {"n_gpus": n_gpus, "seconds": wall_warm, "seconds_first_call": wall_cold,
+                res, wall_first, wall, rel = timed_sweep(gpuprobe.GP_PROBE_ALL_SINGLE)
+                sweep = {"n_gpus": n_gpus, "seconds": wall, "seconds_first_call": wall_first,
+                         "release_after_return_s": rel,
+                         "alloc_wait_s": [round(r.alloc_s, 4) for r in res],
                          "healthy": [int(r.healthy) for r in res],
                          "copy_gbps": [round(r.copy_gbps_median, 1) for r in res],
                          "triad_gbps": [round(r.triad_gbps_median, 1) for r in res],
@@ -486,13 +507,15 @@ def run_ours(args):
                          "verify_gbps": [round(r.verify_gbps_median, 1) for r in res],
                          "gemm_tflops": [round(r.gemm.tflops_median, 1) for r in res],
                          "gemm_max_scaled_err": [r.gemm.max_scaled_err for r in res],
-                         "probes": "copy+triad+pattern(64+2 passes)+gemm, 16 GiB/array"}
+                         "probes": "copy+triad+pattern(64+2 passes)+gemm, 16 GiB/array, cold arena (keep_arena = 0): "
+                                   "gp_probe_all entry to return incl. allocation and result copy-out; the arenas are "
+                                   "released on background threads as the call returns (release_after_return_s)"}
             except gpuprobe.GpuProbeError as e:
                 try:
                     mask3 = gpuprobe.GP_PROBE_COPY | gpuprobe.GP_PROBE_TRIAD | gpuprobe.GP_PROBE_PATTERN
-                    res, wall_cold = p3.probe_all(n_gpus, mask3)
-                    res, wall_warm = p3.probe_all(n_gpus, mask3)
-                    sweep = {"n_gpus": n_gpus, "seconds": wall_warm, "seconds_first_call": wall_cold,
+                    res, wall_first, wall, rel = timed_sweep(mask3)
+                    sweep = {"n_gpus": n_gpus, "seconds": wall, "seconds_first_call": wall_first,
+                             "release_after_return_s": rel,
                              "healthy": [int(r.healthy) for r in res], "probes": "copy+triad+pattern",
                              "note": f"gemm probe unavailable: {e}"}
                 except gpuprobe.GpuProbeError as e2:

@@ -645,15 +645,34 @@ int gp_device_poisoned(gp_ctx* ctx, const char* uuid) {
 int gp_device_reset(gp_ctx* ctx, const char* uuid) {
   Device* d = find_device(ctx, uuid);
   if (!d) { set_error("device '%s' is not visible to CUDA", uuid ? uuid : "(null)"); return ctx ? GP_ERR_NO_DEVICE : GP_ERR_INVALID; }
-  std::lock_guard<std::mutex> multi(ctx->multi_mu);
+  std::lock_guard<std::mutex> multi(ctx->multi_mu);  // no cross-device probe while a context goes away
+  // Everything that points INTO the dying context from outside has to go first: communicators, the peer
+  // mappings the other devices hold on this one, and their arenas' access grants for it.  (Resetting with those
+  // in place crashed inside the driver later, in cuEventDestroy at shutdown: seen on 2 and 8 GPUs.)
+  nccl_teardown(ctx);
+  for (auto& o : ctx->devs) {
+    if (o.get() == d) continue;
+    std::lock_guard<std::mutex> g(o->mu);
+    if (!o->ready && !o->arena) continue;
+    arena_join_reaper(o.get());
+    if (cudaSetDevice(o->ordinal) != cudaSuccess) { (void)cudaGetLastError(); continue; }
+    if (o->stream) cudaStreamSynchronize(o->stream);
+    if (o->peer_mask >> d->ordinal & 1) free_arena(o.get());  // its mapping names the dying device as an accessor
+    (void)cudaDeviceDisablePeerAccess(d->ordinal);             // "not enabled" is the common, harmless answer
+    (void)cudaGetLastError();
+  }
   std::lock_guard<std::mutex> g(d->mu);
   cudaError_t e = cudaSetDevice(d->ordinal);
   (void)e;
+  for (auto& o : ctx->devs)
+    if (o.get() != d) (void)cudaDeviceDisablePeerAccess(o->ordinal);
+  (void)cudaGetLastError();
   // every handle below belongs to the context that is about to die; failures while dropping them are expected
   device_release(d);
   (void)cudaGetLastError();
-  nccl_teardown(ctx);  // communicators hold streams and buffers in the old context
   noalloc_forget_device(d->ordinal);
+  cudaDeviceSynchronize();
+  (void)cudaGetLastError();
   e = cudaDeviceReset();
   if (e != cudaSuccess) {
     set_error("cudaDeviceReset: %s (%d)", cudaGetErrorString(e), (int)e);
