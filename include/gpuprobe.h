@@ -155,6 +155,10 @@ typedef struct gp_config {
   uint32_t gemm_variant;   /* GP_GEMM_*: which tcgen05 kernel the GEMM probe launches */
   uint32_t test_fault;     /* GP_TEST_FAULT_* bits, tests only: make a check see what a broken GPU would produce */
   uint32_t reserved2[2];
+  uint64_t triad_expect_sum;  /* known answer for the triad probe at this hbm_bytes / seed: SUM and XOR (mod 2^64) of the */
+  uint64_t triad_expect_xor;  /* u64 words of a = fmaf(3, c, b), computed OFF the device (the CPU oracle's
+                               * gp_cpu_triad_checksum; INTEGRATION.md lists the default configuration's).  Both 0 ->
+                               * not compared.  triad_ok alone is the GPU checking itself with the same FMA units. */
 } gp_config;
 
 /* One verify pass — SURVEY.md §8(c).  All sums are mod 2^64. */
@@ -229,9 +233,10 @@ typedef struct gp_device_result {
   uint64_t arena_bytes;     /* device memory the call ran in */
   uint32_t arena_reused;    /* 1 if the arena was already there on entry (periodic re-probe of an idle device) */
   uint32_t arena_backend;   /* GP_ARENA_VMM or GP_ARENA_MALLOC actually used */
+  uint64_t triad_sum, triad_xor; /* SUM / XOR of the u64 words of the triad's result array */
+  uint32_t triad_known_answer;   /* 0 not compared (no expectation configured), 1 equal, 2 different (=> TRIAD failed) */
   uint32_t free_deferred;   /* 1 if keep_arena = 0 and the arena is being released on a background thread as the call
                              * returns (the memory is back with the driver a moment later; the next call waits for it) */
-  uint32_t reserved3;
 } gp_device_result;
 
 /* Verdict on the GPU-to-GPU fabric (K4 of SURVEY.md §8): the P2P matrices, their spread, the worst pair and the

@@ -305,7 +305,7 @@ static int copy_probe_locked(Ctx* ctx, Device* d, uint64_t bytes, uint32_t warmu
 }
 
 static int triad_probe_locked(Ctx* ctx, Device* d, uint64_t bytes, uint32_t warmup, uint32_t iters,
-                              gp_timing* t, uint64_t* bad, int64_t* detail) {
+                              gp_timing* t, uint64_t* bad, int64_t* detail, uint64_t* sum_xor = nullptr) {
   if (bytes == 0 || (bytes & ((1u << 20) - 1))) { set_error("triad bytes must be a non-zero multiple of 1 MiB"); return GP_ERR_INVALID; }
   int rc = ensure_arena(ctx, d, 3 * bytes);
   if (rc) return rc;
@@ -329,8 +329,14 @@ static int triad_probe_locked(Ctx* ctx, Device* d, uint64_t bytes, uint32_t warm
   CU_OR_RETURN(launch_triad_check(a, n, seed, s, d->d_count, d->sm_count, d->stream), detail);
   CU_OR_RETURN(cudaMemcpyAsync(d->h_count, d->d_count, sizeof(unsigned long long),
                                cudaMemcpyDeviceToHost, d->stream), detail);
+  // the result's checksum, for the known-answer compare (the check above is the GPU agreeing with itself)
+  CU_OR_RETURN(launch_pattern_verify(reinterpret_cast<const uint64_t*>(a), bytes / 8, kPatNone, 0, d->scratch,
+                                     d->d_results, d->sm_count, d->stream), detail);
+  CU_OR_RETURN(cudaMemcpyAsync(d->h_results, d->d_results, sizeof(gp_pattern_result), cudaMemcpyDeviceToHost,
+                               d->stream), detail);
   CU_OR_RETURN(cudaStreamSynchronize(d->stream), detail);
   if (bad) *bad = *d->h_count;
+  if (sum_xor) { sum_xor[0] = d->h_results[0].sum; sum_xor[1] = d->h_results[0].xor_; }
   return GP_OK;
 }
 
@@ -465,10 +471,17 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
   }
   if (mask & GP_PROBE_TRIAD) {
     uint64_t bad = 0;
-    rc = triad_probe_locked(ctx, d, hbm, warmup, iters, &out->triad_t, &bad, &out->detail);
+    uint64_t sx[2] = {0, 0};
+    rc = triad_probe_locked(ctx, d, hbm, warmup, iters, &out->triad_t, &bad, &out->detail, sx);
     if (rc) return fail(rc);
     out->probed_mask |= GP_PROBE_TRIAD;
     out->triad_ok = bad == 0;
+    out->triad_sum = sx[0];
+    out->triad_xor = sx[1];
+    if (ctx->cfg.triad_expect_sum || ctx->cfg.triad_expect_xor) {
+      out->triad_known_answer = (sx[0] == ctx->cfg.triad_expect_sum && sx[1] == ctx->cfg.triad_expect_xor) ? 1 : 2;
+      if (out->triad_known_answer == 2) out->failed_mask |= GP_PROBE_TRIAD;
+    }
     out->triad_gbps_best = gbps(3.0 * hbm, out->triad_t.best_ms);
     out->triad_gbps_median = gbps(3.0 * hbm, out->triad_t.median_ms);
     if (!out->triad_ok || (ctx->cfg.min_triad_gbps > 0 && out->triad_gbps_median < ctx->cfg.min_triad_gbps))

@@ -54,6 +54,8 @@ type Options struct {
 	MaxP2PSpread          float64
 	MinAllreduceBusbwGBps float64
 	FabricBytes           uint64
+	TriadExpectSum        uint64        // known answer of the triad at HbmBytes (INTEGRATION.md §2); 0, 0 = not compared
+	TriadExpectXor        uint64
 	KeepArena             bool          // keep an idle device's arena between re-probes; Allocate trims it
 	SliceBinary           string        // path of gpuprobe-slice; "" disables MIG / isolated probes
 	ChildTimeout          time.Duration // 0 -> 120 s
@@ -129,6 +131,8 @@ func NewProbe(o Options) (*Probe, error) {
 	cfg.max_p2p_spread = C.double(o.MaxP2PSpread)
 	cfg.min_allreduce_busbw_gbps = C.double(o.MinAllreduceBusbwGBps)
 	cfg.fabric_bytes = C.uint64_t(o.FabricBytes)
+	cfg.triad_expect_sum = C.uint64_t(o.TriadExpectSum)
+	cfg.triad_expect_xor = C.uint64_t(o.TriadExpectXor)
 	var ctx *C.gp_ctx
 	// gp_last_error_detail() is thread-local in the library: the goroutine must stay on the OS thread
 	// that made the failing call until the text has been fetched.

@@ -62,6 +62,7 @@ class Config(C.Structure):
         ("min_allreduce_busbw_gbps", C.c_double), ("fabric_bytes", C.c_uint64),
         ("arena_backend", C.c_uint32), ("sm_limit", C.c_uint32),
         ("gemm_variant", C.c_uint32), ("test_fault", C.c_uint32), ("reserved2", C.c_uint32 * 2),
+        ("triad_expect_sum", C.c_uint64), ("triad_expect_xor", C.c_uint64),
     ]
 
 
@@ -108,7 +109,8 @@ class DeviceResult(C.Structure):
         ("pattern_digest", C.c_uint64), ("gemm", GemmResult),
         ("alloc_s", C.c_double), ("free_s", C.c_double), ("kernels_s", C.c_double),
         ("arena_bytes", C.c_uint64), ("arena_reused", C.c_uint32), ("arena_backend", C.c_uint32),
-        ("free_deferred", C.c_uint32), ("reserved3", C.c_uint32),
+        ("triad_sum", C.c_uint64), ("triad_xor", C.c_uint64), ("triad_known_answer", C.c_uint32),
+        ("free_deferred", C.c_uint32),
     ]
 
 

@@ -32,6 +32,7 @@ struct ProbeConfig {
   uint64_t FabricBytes = 0;          // 0 = 1 GiB per transfer
   bool KeepArena = false;            // keep the arena of an idle device mapped between re-probes (freed in Allocate)
   bool Isolate = false;              // every periodic re-probe of a full GPU from a child process
+  uint64_t TriadExpectSum = 0, TriadExpectXor = 0;  // known answer of the triad at HbmBytes (hex in the file); 0 0 = none
 };
 struct Config {
   std::string WebListenAddress = "9002";  // config.go:17 (no colon — the reference's own default)
@@ -57,6 +58,8 @@ struct Config {
     c.min_allreduce_busbw_gbps = Probe.MinAllreduceBusbwGbps;
     c.fabric_bytes = Probe.FabricBytes;
     c.keep_arena = Probe.KeepArena ? 1u : 0u;
+    c.triad_expect_sum = Probe.TriadExpectSum;
+    c.triad_expect_xor = Probe.TriadExpectXor;
     return c;
   }
 };
@@ -122,6 +125,8 @@ inline Config LoadConfig(const std::string& yamlText) {
   if (auto v = get("probe.fabricBytes")) c.Probe.FabricBytes = std::stoull(*v);
   if (auto v = get("probe.keepArena")) c.Probe.KeepArena = truthy(*v);
   if (auto v = get("probe.isolate")) c.Probe.Isolate = truthy(*v);
+  if (auto v = get("probe.triadExpectSum")) c.Probe.TriadExpectSum = std::stoull(*v, nullptr, 0);
+  if (auto v = get("probe.triadExpectXor")) c.Probe.TriadExpectXor = std::stoull(*v, nullptr, 0);
   return c;
 }
 

@@ -372,6 +372,8 @@ int main() {
     Config f3 = LoadConfig("probe:\n  minP2PGbps: 600\n  maxP2PSpread: 1.2\n  minAllreduceBusbwGbps: 500\n  fabricBytes: 268435456\n  keepArena: true\n  isolate: true\n  fabric: false\n");
     gp_config fg = f3.ToGpConfig();
     CHECK(fg.min_p2p_gbps == 600 && fg.max_p2p_spread == 1.2 && fg.min_allreduce_busbw_gbps == 500 && fg.fabric_bytes == (256ull << 20) && fg.keep_arena == 1);
+    Config k3 = LoadConfig("probe:\n  triadExpectSum: 0xb4e518db1999320e\n  triadExpectXor: 0xb4fb50e5795c70ba\n");
+    CHECK(k3.ToGpConfig().triad_expect_sum == 0xb4e518db1999320eull && k3.ToGpConfig().triad_expect_xor == 0xb4fb50e5795c70baull);
     CHECK(f3.Probe.Isolate && !f3.Probe.Fabric && LoadConfig("").Probe.Fabric && LoadConfig("").ToGpConfig().keep_arena == 0);
   }
   printf("host_selftest ok\n");

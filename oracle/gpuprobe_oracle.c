@@ -323,3 +323,43 @@ ORACLE_EXPORT int gp_cpu_hbm_step(void* arena, uint64_t bytes, uint32_t step, ui
   j.op = 2; j.src = (const uint64_t*)Z; j.kind = -1; j.pass = 0; run_step_op(j, nw, nthreads, &out[2]);
   return 0;
 }
+
+/* Known answer for the triad probe: SUM and XOR (mod 2^64) of the u64 words of a[i] = fmaf(s, c[i], b[i]) with b, c
+ * from the counter generator — what the device leaves in `a`, folded exactly as the verify kernel folds it.  Streaming
+ * (nothing is stored), so the 16 GiB default configuration can be computed on any host.  The device grades its own
+ * triad with the same fmaf on the same chip; comparing against THIS number is what would catch a broken FMA. */
+typedef struct { uint64_t seed, i0, i1; float s; uint64_t sum, xr; } triad_ck_job;
+static void* triad_ck_run(void* p) {
+  triad_ck_job* j = (triad_ck_job*)p;
+  uint64_t sum = 0, xr = 0;
+  for (uint64_t w = j->i0; w < j->i1; ++w) {
+    uint32_t lo, hi;
+    const float a0 = fmaf(j->s, gen_f32(j->seed ^ 0x2222222222222222ull, 2 * w), gen_f32(j->seed ^ 0x1111111111111111ull, 2 * w));
+    const float a1 = fmaf(j->s, gen_f32(j->seed ^ 0x2222222222222222ull, 2 * w + 1), gen_f32(j->seed ^ 0x1111111111111111ull, 2 * w + 1));
+    memcpy(&lo, &a0, 4);
+    memcpy(&hi, &a1, 4);
+    const uint64_t word = (uint64_t)lo | ((uint64_t)hi << 32);
+    sum += word;
+    xr ^= word;
+  }
+  j->sum = sum;
+  j->xr = xr;
+  return NULL;
+}
+ORACLE_EXPORT void gp_cpu_triad_checksum(uint64_t seed, uint64_t nfloats, float s, int nthreads, uint64_t* sum, uint64_t* xr) {
+  if (nthreads < 1) nthreads = 1;
+  if (nthreads > 256) nthreads = 256;
+  const uint64_t nwords = nfloats / 2;
+  pthread_t th[256];
+  triad_ck_job jobs[256];
+  for (int t = 0; t < nthreads; ++t) {
+    jobs[t].seed = seed; jobs[t].s = s;
+    jobs[t].i0 = nwords * (uint64_t)t / (uint64_t)nthreads;
+    jobs[t].i1 = nwords * (uint64_t)(t + 1) / (uint64_t)nthreads;
+    pthread_create(&th[t], NULL, triad_ck_run, &jobs[t]);
+  }
+  uint64_t S = 0, X = 0;
+  for (int t = 0; t < nthreads; ++t) { pthread_join(th[t], NULL); S += jobs[t].sum; X ^= jobs[t].xr; }
+  *sum = S;
+  *xr = X;
+}

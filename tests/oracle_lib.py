@@ -66,6 +66,8 @@ def load():
     lib.gp_cpu_gemm_ref.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
     lib.gp_cpu_gemm_sample.restype = C.c_double
     lib.gp_cpu_gemm_sample.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, P(C.c_double)]
+    lib.gp_cpu_triad_checksum.restype = None
+    lib.gp_cpu_triad_checksum.argtypes = [C.c_uint64, C.c_uint64, C.c_float, C.c_int, P(C.c_uint64), P(C.c_uint64)]
     lib.gp_cpu_hbm_step.restype = C.c_int
     lib.gp_cpu_hbm_step.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_int, C.c_int, P(PatternResult)]
     _lib = lib
@@ -112,3 +114,10 @@ def hbm_step(lib, arena, nbytes, step, seed=0x5EED, gen=True, nthreads=1):
     rc = lib.gp_cpu_hbm_step(arena.ctypes.data, nbytes, step, seed, int(gen), nthreads, out)
     assert rc == 0, rc
     return list(out)
+
+
+def triad_checksum(lib, seed, nfloats, s=3.0, nthreads=1):
+    """(sum, xor) of the u64 words of a = fmaf(s, c, b) over the generator's b and c — the triad probe's known answer."""
+    a, b = C.c_uint64(), C.c_uint64()
+    lib.gp_cpu_triad_checksum(seed, nfloats, s, nthreads, C.byref(a), C.byref(b))
+    return a.value, b.value

@@ -225,3 +225,20 @@ def test_golden_stream_gemm_fixtures(oracle):
             ad = C.c_double()
             v = oracle.gp_cpu_gemm_sample(g["seed"], g["mnk"], pt["i"], pt["j"], C.byref(ad))
             assert v == pt["ref"] and ad.value == pt["absdot"]
+
+
+def test_triad_known_answer_streaming_matches_stored_and_golden(oracle):
+    """gp_cpu_triad_checksum (nothing stored) against the stored-array port of the step, and against the committed
+    known answers (tests/golden/triad_known_answers.json) at the smallest size."""
+    import json
+    import os
+    import oracle_lib
+    n = 1 << 18
+    arena = np.zeros(5 * n * 4, dtype=np.uint8)
+    out = oracle_lib.hbm_step(oracle, arena, n * 4, step=0, nthreads=2)
+    for threads in (1, 3, 8):
+        assert oracle_lib.triad_checksum(oracle, 0x5EED, n, 3.0, nthreads=threads) == (out[2].sum, out[2].xor_)
+    assert oracle_lib.triad_checksum(oracle, 0x5EED + 1, n, 3.0) != (out[2].sum, out[2].xor_)
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "triad_known_answers.json")))
+    k = gold["answers"][str(64 << 20)]
+    assert oracle_lib.triad_checksum(oracle, 0x5EED, (64 << 20) // 4, 3.0, nthreads=4) == (int(k["sum"], 16), int(k["xor"], 16))

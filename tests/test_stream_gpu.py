@@ -116,3 +116,34 @@ def test_triad_golden_fixture_on_gpu(probe):
     for t in gold["triad"]:
         out = probe.hbm_step(DEV, t["nbytes"], step=0)
         assert (hex(out[2].sum), hex(out[2].xor_), hex(out[2].wsum)) == (t["sum"], t["xor"], t["wsum"])
+
+
+def test_triad_known_answer_from_the_cpu_oracle(oracle):
+    """triad_ok is the GPU agreeing with itself (same fmaf, same chip): fine for memory faults, blind to a
+    broken FMA.  The known answer closes that: SUM / XOR of the result's words computed OFF the device by the
+    oracle's streaming gp_cpu_triad_checksum, handed in through gp_config, compared by the probe."""
+    nbytes = 64 << 20
+    esum, exor = oracle_lib.triad_checksum(oracle, 0x5EED, nbytes // 4, 3.0, nthreads=4)
+    kw = dict(hbm_bytes=nbytes, iters=2, warmup=1)
+    with gpuprobe.Probe(**kw) as p:                                     # nothing configured: reported, not compared
+        r = p.probe_device("0", gpuprobe.GP_PROBE_TRIAD)
+        assert (r.triad_sum, r.triad_xor) == (esum, exor) and r.triad_known_answer == 0 and r.healthy == 1
+    with gpuprobe.Probe(triad_expect_sum=esum, triad_expect_xor=exor, **kw) as p:
+        r = p.probe_device("0", gpuprobe.GP_PROBE_TRIAD)
+        assert r.triad_known_answer == 1 and r.triad_ok == 1 and r.healthy == 1
+    with gpuprobe.Probe(triad_expect_sum=esum ^ 1, triad_expect_xor=exor, **kw) as p:   # a device whose FMA is off by a bit
+        r = p.probe_device("0", gpuprobe.GP_PROBE_TRIAD)
+        assert r.triad_known_answer == 2 and r.triad_ok == 1 and r.healthy == 0
+        assert r.failed_mask == gpuprobe.GP_PROBE_TRIAD
+
+
+def test_triad_known_answer_default_configuration():
+    """The 16 GiB / seed 0x5EED constant committed in tests/golden/triad_known_answers.json (made by
+    tests/golden/make_triad_known_answers.py on the CPU) against the device at the full default size."""
+    import json
+    import os
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "triad_known_answers.json")))
+    k = gold["answers"]["17179869184"]
+    with gpuprobe.Probe(iters=2, warmup=1, triad_expect_sum=int(k["sum"], 16), triad_expect_xor=int(k["xor"], 16)) as p:
+        r = p.probe_device("0", gpuprobe.GP_PROBE_TRIAD)
+        assert r.hbm_bytes == 16 << 30 and r.triad_known_answer == 1 and r.healthy == 1
