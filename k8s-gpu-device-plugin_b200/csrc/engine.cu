@@ -413,7 +413,10 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
   };
   auto run_gemm = [&](uint8_t* workspace, const std::function<void()>* after_timed) -> int {
     const uint64_t seed = ctx->cfg.seed ? ctx->cfg.seed : 0x5EEDull;
-    int r = gemm_probe_locked(ctx, d, gemm_mnk, seed, warmup, iters, gemm_samples, &out->gemm, workspace, after_timed);
+    // The GEMM is the first thing this call runs on a GPU that may have sat idle: give the clocks a few
+    // milliseconds of tensor work to settle before anything is timed (8 launches at 8192^3 = 5.5 ms).
+    const uint32_t gemm_warmup = std::max<uint32_t>(warmup, 8);
+    int r = gemm_probe_locked(ctx, d, gemm_mnk, seed, gemm_warmup, iters, gemm_samples, &out->gemm, workspace, after_timed);
     if (r) return r;
     out->probed_mask |= GP_PROBE_GEMM;
     if (out->gemm.samples_bad ||

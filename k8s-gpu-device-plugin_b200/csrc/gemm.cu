@@ -45,7 +45,13 @@ constexpr int kBlockM = 128;  // rows of A (and of the accumulator) per CTA
 constexpr int kBlockK = 64;   // 64 bf16 = 128 bytes = one swizzle span
 constexpr int kUmmaK = 16;    // K per tcgen05.mma for 16-bit inputs
 constexpr int kTileN = 256;   // accumulator columns per tile (UMMA N)
-constexpr int kEpiWarps = 8;   // two sets of four (one warp per TMEM lane quarter per set)
+#ifndef GP_GEMM_EPI_WARPS
+#define GP_GEMM_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = GP_GEMM_EPI_WARPS;  // sets of four (one warp per TMEM lane quarter per set)
+constexpr int kEpiSets = kEpiWarps / 4;
+constexpr int kSetCols = kTileN / kEpiSets;   // columns of every 256-column half one set drains
+static_assert(kEpiWarps % 4 == 0 && kSetCols % 64 == 0, "whole sets, whole 64-column steps");
 constexpr int kGemmThreads = 32 * (2 + kEpiWarps);
 
 // CG = CTAs per MMA (tcgen05 cta_group), NT = 256-wide N sub-tiles accumulated per tile.
@@ -401,7 +407,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else {
     // ============================== epilogue ==============================
     const int quarter = warp & 3;       // a warp may only touch TMEM lanes [32 q, 32 q + 32)
-    const int set = (warp - 2) >> 2;    // which 128 columns of every 256-column half this warp drains
+    const int set = (warp - 2) >> 2;    // which kSetCols columns of every 256-column half this warp drains
     const uint32_t tempty_leader = CG == 2 ? map_to_cta(tempty_bar(0), 0) : tempty_bar(0);
     const uint64_t pol_c = l2_policy((hints >> 4) & 3);
     int acc = 0; uint32_t acc_phase = 0;  // NT == 1: accumulator stage of this tile; NT == 2: phase only
@@ -414,8 +420,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const int b = NT == 2 ? h : acc;  // TMEM half == barrier index
         mbar_wait_addr(tfull_bar(b), acc_phase);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(b * kTileN + set * 128);
-        const size_t col0 = (size_t)tn * Cfg::kTileNAll + (size_t)(h * kTileN + set * 128);
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(b * kTileN + set * kSetCols);
+        const size_t col0 = (size_t)tn * Cfg::kTileNAll + (size_t)(h * kTileN + set * kSetCols);
         // release the half as soon as its last chunk is in registers; the stores that follow no longer hold it
         auto release_half = [&] {
           tc_fence_before();
@@ -430,9 +436,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           float v[2][32];
           tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
+          for (int c = 0; c < kSetCols / 32; ++c) {
             tmem_ld_wait();
-            if (c + 1 < 4) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
+            if (c + 1 < kSetCols / 32) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
             else release_half();
 #pragma unroll
             for (int q = 0; q < 4; ++q) st_f8_hint(crow + c * 32 + q * 8, v[c & 1] + 8 * q, pol_c);
@@ -443,9 +449,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           tmem_ld_32x32(taddr, v[0]);
           tmem_ld_32x32(taddr + 32u, v[0] + 32);
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
+          for (int c = 0; c < kSetCols / 64; ++c) {
             tmem_ld_wait();
-            if (c + 1 < 2) {
+            if (c + 1 < kSetCols / 64) {
               tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 64), v[(c + 1) & 1]);
               tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 64 + 32), v[(c + 1) & 1] + 32);
             } else {

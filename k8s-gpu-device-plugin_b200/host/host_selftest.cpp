@@ -326,6 +326,30 @@ int main() {
     t.join();
     CHECK(got.size() == 3 && health_of(got[1], "GPU-n0") == "Unhealthy" && health_of(got[2], "GPU-n0") == "Healthy");
   }
+  // --- Start(): blocks instead of spinning, serves restarts, returns when stopped (the reference's loop does neither) ---
+  {
+    FakeBackend fb;
+    ProbeMetrics pm;
+    PluginManager mgr(MigStrategySingle, {Resource::New("*", "gpu")}, [&] { return nodes; }, &fb, &pm, GP_PROBE_ALL_SINGLE);
+    mgr.EnableFabric(false);
+    Error start_err = std::string("not returned");
+    std::thread runner([&] { start_err = mgr.Start(); });
+    for (int i = 0; i < 200 && !mgr.running(); ++i) std::this_thread::sleep_for(std::chrono::milliseconds(5));
+    CHECK(mgr.running() && mgr.loads() == 1);
+    std::this_thread::sleep_for(std::chrono::milliseconds(50));
+    CHECK(mgr.wakeups() == 0);                       // idle means asleep: no `default:` arm spinning a core
+    mgr.Restart();
+    for (int i = 0; i < 200 && mgr.loads() < 2; ++i) std::this_thread::sleep_for(std::chrono::milliseconds(5));
+    CHECK(mgr.loads() == 2 && mgr.wakeups() == 1);   // one wake-up per request, flag consumed once
+    auto plug0 = mgr.plugins()[0];
+    std::thread law([&] { plug0->ListAndWatch([](const std::vector<PluginDevice>&) { return true; }); });
+    mgr.Stop();
+    runner.join();                                   // Start() returns after stopping the plugins ...
+    law.join();                                      // ... whose ListAndWatch streams have ended
+    CHECK(!start_err && !mgr.running());
+    PluginManager bad(MigStrategyNone, {Resource::New("GPU", "gpu")}, [&] { return nodes; }, &fb, &pm, 1);
+    CHECK(bad.Start().value() == "GPU name 'NVIDIA B200' does not match any resource patterns");  // load errors come back, not a hang
+  }
   // --- preferred allocation ---
   {
     Devices reps;

@@ -258,8 +258,40 @@ class PluginManager {
   void EnableFabric(bool on) { fabric_enabled_ = on; }
   const gp_fabric_result& fabric() const { return fabric_; }
   const P2PMatrix& fabricMatrix() const { return fabric_matrix_; }
-  // manager.go:108-110 sets a flag that the Start loop polls (manager.go:93-97); here the poll is explicit
-  void Restart() { restart_ = true; }
+  // plugin/manager.go:56-99 Start(): load, serve restart requests until told to stop, stop the plugins, RETURN.
+  // The reference's loop has a `default:` arm, so it busy-spins a core (manager.go:89-97), reads an unsynchronised
+  // `restart` flag (manager.go:94 vs :109) and does not return after ctx.Done().  This is the minimal fix the Go
+  // side needs as well: block until there is something to do, atomic flag, return at the end.
+  Error Start() {
+    if (auto e = loadPlugins()) return e;
+    std::unique_lock<std::mutex> lk(run_mu_);
+    running_ = true;
+    for (;;) {
+      run_cv_.wait(lk, [this] { return stop_requested_ || restart_.load(); });
+      ++wakeups_;
+      if (stop_requested_) break;
+      restart_ = false;
+      lk.unlock();
+      if (auto e = restartPlugins()) { lk.lock(); running_ = false; return e; }
+      lk.lock();
+    }
+    lk.unlock();
+    { std::lock_guard<std::mutex> g(mu_); for (auto& p : plugins_) p->Stop(); }
+    lk.lock();
+    running_ = false;
+    return std::nullopt;
+  }
+  void Stop() {
+    { std::lock_guard<std::mutex> g(run_mu_); stop_requested_ = true; }
+    run_cv_.notify_all();
+  }
+  bool running() { std::lock_guard<std::mutex> g(run_mu_); return running_; }
+  int wakeups() const { return wakeups_; }
+  // manager.go:108-110 sets a flag that the Start loop consumes; poll() is the same thing for callers without a loop
+  void Restart() {
+    { std::lock_guard<std::mutex> g(run_mu_); restart_ = true; }
+    run_cv_.notify_all();
+  }
   Error poll() {
     if (!restart_.exchange(false)) return std::nullopt;
     return restartPlugins();
@@ -429,6 +461,10 @@ class PluginManager {
   gp_fabric_result fabric_{};
   P2PMatrix fabric_matrix_;
   std::atomic<int> isolated_probes_{0}, not_graded_{0};
+  std::mutex run_mu_;
+  std::condition_variable run_cv_;
+  bool stop_requested_ = false, running_ = false;
+  std::atomic<int> wakeups_{0};
   std::thread ticker_;
   std::mutex tick_mu_;
   std::condition_variable tick_cv_;
