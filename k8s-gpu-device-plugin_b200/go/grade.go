@@ -117,6 +117,16 @@ func (e HealthEvent) Health() string {
 	return pluginapi.Unhealthy
 }
 
+// ApplyHealth is the ListAndWatch arm's half (go/startup_fixes.patch, plugin/plugin.go:181): write the verdict
+// under the mutex, report whether it was a transition.  Twin: the locked block of NvidiaDevicePlugin::ListAndWatch.
+func ApplyHealth(ev HealthEvent) (changed bool) {
+	healthMu.Lock()
+	defer healthMu.Unlock()
+	changed = ev.Device.Health != ev.Health()
+	ev.Device.Health = ev.Health()
+	return changed
+}
+
 // Report delivers ev without ever blocking.  If the buffer is full (nobody has been listening for
 // a long time) the verdict is applied to the device directly, so the first list of the next
 // ListAndWatch stream (plugin/plugin.go:174) already carries it.
