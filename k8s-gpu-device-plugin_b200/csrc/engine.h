@@ -57,8 +57,19 @@ struct Device {
   uint64_t triad_operands_seed = 0;
 };
 
+// host-side fp64 reference of the GEMM probe's sampled entries: a pure function of (seed, shape, sample count),
+// so it is computed once per context and shared by every device and every later probe (gemm.cu)
+struct GemmRef {
+  uint64_t seed = 0;
+  uint32_t m = 0, n = 0, k = 0, samples = 0;
+  std::vector<uint32_t> ij;        // 2 * samples: row, column
+  std::vector<double> acc, aacc;   // sum_k a*b and sum_k |a*b| per sample
+};
+
 struct Ctx {
   gp_config cfg;
+  std::mutex gemm_ref_mu;
+  std::vector<std::shared_ptr<GemmRef>> gemm_refs;
   std::vector<std::unique_ptr<Device>> devs;
   std::mutex multi_mu;  // serialises the cross-device probes (P2P, NCCL)
   void* nccl_handle = nullptr;

@@ -163,3 +163,14 @@ def test_gemm_bf16_output_is_checked_bit_exact():
         g = p.gemm_probe(DEV, mnk=1024, iters=1, warmup=0, samples=1024)
         assert g.bf16_mismatches == 1 and g.samples_bad == 1
         assert g.max_scaled_err <= TOL and g.freivalds_err <= TOL   # the fp32 run itself is clean
+
+
+def test_gemm_reference_cache_is_keyed_by_seed_shape_and_samples():
+    """The host fp64 reference of the sampled entries is computed once per context and reused; a different seed,
+    shape or sample count must get its own (a stale reference would show as thousands of bad samples)."""
+    with gpuprobe.Probe(keep_arena=1) as p:
+        for seed, mnk, samples in [(1, 1024, 512), (2, 1024, 512), (1, 1024, 512), (1, 2048, 512), (1, 1024, 1024),
+                                   (2, 1024, 512), (3, 512, 64), (4, 512, 64), (5, 512, 64), (6, 512, 64),
+                                   (7, 512, 64), (8, 512, 64), (9, 512, 64), (1, 1024, 512)]:  # > 8 keys: eviction too
+            g = p.gemm_probe(DEV, mnk=mnk, seed=seed, iters=1, warmup=0, samples=samples)
+            assert g.samples == samples and g.samples_bad == 0 and g.max_scaled_err <= TOL, (seed, mnk, samples)

@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
 """Full-box health sweep timing: gp_probe_all on 1..N GPUs in one process (the plugin's shape),
-cold arena (malloc+free inside) and warm arena.  Writes gpurun_out/sweep_<n>.json."""
+cold arena (allocated inside; released on background threads as the call returns, and given time to arrive
+before the next repetition: gp_trim) and warm arena.  Writes gpurun_out/sweep_<n>.json."""
 import json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "k8s-gpu-device-plugin_b200"))
@@ -14,7 +15,10 @@ for n in [k for k in (1, 2, 4, 8) if k <= nmax]:
     rows = []
     for rep in range(3):
         res, wall = p.probe_all(n, gpuprobe.GP_PROBE_ALL_SINGLE)
-        rows.append({"wall_s": wall, "per_device_s": [round(r.duration_s, 3) for r in res], "healthy": [r.healthy for r in res],
+        t1 = time.time()
+        p.trim()
+        rows.append({"wall_s": wall, "release_after_return_s": round(time.time() - t1, 4),
+                     "alloc_wait_s": [round(r.alloc_s, 4) for r in res], "per_device_s": [round(r.duration_s, 3) for r in res], "healthy": [r.healthy for r in res],
                      "copy": [round(r.copy_gbps_median) for r in res], "triad": [round(r.triad_gbps_median) for r in res],
                      "fill": [round(r.fill_gbps_median) for r in res], "verify": [round(r.verify_gbps_median) for r in res],
                      "gemm": [round(r.gemm.tflops_median) for r in res]})
