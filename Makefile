@@ -47,4 +47,13 @@ clean:
 	rm -f $(OBJS) $(CSRC)/*.ptxas.log $(LIB) $(DEVLIB) $(HOST)/host_selftest $(HOST)/gpuprobe-slice $(HOST)/plugin_sim
 	$(MAKE) -C oracle clean
 
-.PHONY: all oracle host clean dev
+# development sweeps (not part of `all`): launch shapes, peer-write store shapes, allocator timing
+tools: tools/hbm_sweep tools/p2p_write_sweep tools/vmm_timing
+tools/hbm_sweep: tools/hbm_sweep.cu
+	$(NVCC) -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -o $@ $<
+tools/p2p_write_sweep: tools/p2p_write_sweep.cu
+	$(NVCC) -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o $@ $<
+tools/vmm_timing: tools/vmm_timing.cu
+	$(NVCC) -O2 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o $@ $< -L/usr/local/cuda/lib64/stubs -lcuda
+
+.PHONY: all oracle host clean dev tools
