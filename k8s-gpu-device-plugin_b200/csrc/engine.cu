@@ -425,7 +425,8 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
     return GP_OK;
   };
   bool gemm_done = false;
-  if ((mask & GP_PROBE_GEMM) && hbm_need > 4 * gemm_need && hbm_need > d->arena_bytes && d->cc_major == 10) {
+  // (not with whole-memory grading: there the arena is sized to the last free GiB and a second buffer would not fit)
+  if ((mask & GP_PROBE_GEMM) && !pat_all && hbm_need > 4 * gemm_need && hbm_need > d->arena_bytes && d->cc_major == 10) {
     // Cold arena and a GEMM to run: the GEMM gets a small buffer of its own (a millisecond to allocate); once its
     // timed launches are over a helper thread allocates the big arena while the GEMM's checks run (Freivalds on
     // the device, 4096 fp64 dot products on the host: tens of milliseconds), so the allocator's latency — and the

@@ -102,6 +102,11 @@ def test_whole_memory_grading():
         assert r.healthy == 1 and r.pattern_passes == 4 and r.pattern_mismatches == 0
         assert r.pattern_bytes > (100 << 30) and r.pattern_bytes % (1 << 20) == 0  # most of the 180 GB card
         assert r.verify_gbps_best > 1000 and r.fill_gbps_best > 1000
+    # with every probe selected the GEMM shares the one big arena (no second buffer beside a card-sized one)
+    with gpuprobe.Probe(pattern_bytes=gpuprobe.GP_PATTERN_ALL_FREE, wo_passes=1, hbm_bytes=1 << 30, iters=2, warmup=1,
+                        gemm_mnk=2048) as p:
+        r = p.probe_device("0", gpuprobe.GP_PROBE_ALL_SINGLE)
+        assert r.healthy == 1 and r.probed_mask == gpuprobe.GP_PROBE_ALL_SINGLE and r.pattern_bytes > (100 << 30)
 
 
 @pytest.mark.parametrize("backend", [gpuprobe.GP_ARENA_VMM, gpuprobe.GP_ARENA_MALLOC, gpuprobe.GP_ARENA_AUTO],
