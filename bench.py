@@ -276,6 +276,17 @@ def fabric_leg(gpuprobe, n, nbytes):
             ar["busbw_gbps"] = bus
             good = [v for v in bus.values() if isinstance(v, float)]
             ar["busbw_peak_gbps"] = max(good) if good else None
+            # n = 2, 4, 8 — the smaller rank counts at the two largest sizes
+            sub = {}
+            for nr in (2, 4):
+                if nr < n:
+                    try:
+                        sub[str(nr)] = {str(sz): round(p.probe_allreduce(nr, sz, warmup=2, iters=5)[1], 1)
+                                        for sz in (1 << 30, 4 << 30)}
+                    except gpuprobe.GpuProbeError as e:
+                        sub[str(nr)] = f"error: {e}"
+            if sub:
+                ar["busbw_gbps_by_ranks"] = sub
             out["allreduce"] = ar
     except gpuprobe.GpuProbeError as e:
         out.setdefault("p2p", {})["error"] = str(e)

@@ -212,6 +212,18 @@ void free_arena_deferred(Device* d) {
   });
 }
 
+// the same for plain cudaMalloc buffers that are not the arena (the cold probe's slabs)
+void free_buffers_deferred(Device* d, const std::vector<void*>& ptrs) {
+  arena_join_reaper(d);
+  if (ptrs.empty()) return;
+  const int ordinal = d->ordinal;
+  d->reaper = std::thread([ptrs, ordinal] {
+    cudaSetDevice(ordinal);
+    for (void* p : ptrs) cudaFree(p);
+    (void)cudaGetLastError();
+  });
+}
+
 void free_arena(Device* d) {
   arena_join_reaper(d);
   if (!d->arena) { d->arena_bytes = 0; d->triad_operands_bytes = 0; return; }

@@ -97,6 +97,7 @@ int device_prepare(Ctx* ctx, Device* d);                  // lazy per-device ini
 int ensure_arena(Ctx* ctx, Device* d, size_t bytes, bool ignore_cap = false);  // lock held
 void free_arena(Device* d);
 void free_arena_deferred(Device* d);         // same, on a reaper thread; returns at once
+void free_buffers_deferred(Device* d, const std::vector<void*>& ptrs);
 void arena_join_reaper(Device* d);
 void release_arena_va(Device* d);            // at shutdown / reset: give the virtual range back too
 // make d's mapped arena readable and writable from the devices in `ordinal_mask` (VMM memory is not
