@@ -18,8 +18,10 @@
  *   - caller owns every output buffer; the library never retains a caller
  *     pointer past the call (cgo rule: no Go pointers held by C).
  *   - the library owns gp_ctx and all device memory.
- *   - every entry point is blocking, takes the per-device lock, and calls
- *     cudaSetDevice on entry: safe from arbitrary OS threads (cgo calls land
+ *   - every entry point is blocking (one exception: with keep_arena = 0 a probe
+ *     returns while its device memory is still being released on a background
+ *     thread; anything that needs the allocator on that device waits for it),
+ *     takes the per-device lock, and calls cudaSetDevice on entry: safe from arbitrary OS threads (cgo calls land
  *     on arbitrary threads).  Calls for DIFFERENT devices run concurrently;
  *     calls for the same device serialise.
  *   - no stdout/stderr, no signals, no exit().
@@ -115,10 +117,11 @@ enum {
 
 /* arena backends (gp_config.arena_backend) */
 enum {
-  GP_ARENA_AUTO = 0,   /* VMM when the driver offers it, else cudaMalloc */
-  GP_ARENA_VMM = 1,    /* one reserved virtual range per device, physical chunks (cuMemCreate) mapped as the
+  GP_ARENA_AUTO = 0,   /* keep_arena = 1: VMM when the driver offers it; keep_arena = 0: cudaMalloc (cheapest cold) */
+  GP_ARENA_VMM = 1,    /* one reserved virtual range per device, 4 GiB physical chunks (cuMemCreate) mapped as the
                         * arena grows: growing never moves or re-allocates what is already mapped */
-  GP_ARENA_MALLOC = 2  /* one cudaMalloc per size change (round-1 behaviour) */
+  GP_ARENA_MALLOC = 2  /* cudaMalloc: one allocation per size change for a kept arena; for a cold gp_probe_device
+                        * (keep_arena = 0) three slabs allocated in order behind the probes that do not need them yet */
 };
 #define GP_FABRIC_MAX_GPUS 16
 
@@ -135,7 +138,8 @@ typedef struct gp_config {
   uint32_t wo_passes;      /* walking-ones passes [0,64]; 0 -> 64 */
   uint32_t gemm_samples;   /* sampled C entries checked on the host in fp64; 0 -> 4096 */
   uint32_t stream_variant; /* GP_STREAM_* */
-  uint32_t keep_arena;     /* 1: keep device memory between probes; 0: free after gp_probe_* */
+  uint32_t keep_arena;     /* 1: keep device memory between probes (gp_trim / gp_trim_device give it back);
+                            * 0: gp_probe_* hand it to a release thread as they return */
   uint32_t gemm_output;    /* GEMM probe's C: 0 = fp32 (strictest check), 1 = bf16 (what cuBLAS bf16 peaks are quoted on) */
   uint64_t seed;           /* GEMM / triad operand generator seed; 0 -> 0x5EED */
   double min_copy_gbps;    /* health floors; 0 -> not enforced */

@@ -424,12 +424,15 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
     if (mask & GP_PROBE_TRIAD) slabs.bytes[2] = hbm;
   }
   uint64_t slab_total = 0;
+  void* gemm_ws = nullptr;  // the GEMM's own buffer in slab mode; released with the slabs (a cudaFree here would
+                            // queue behind every other GPU's slab allocation: the driver serialises them)
 
   auto finish = [&] {
     if (slabs.provider.joinable()) slabs.provider.join();
     if (use_slabs) {
       std::vector<void*> ptrs;
       for (void* q : slabs.p) if (q) ptrs.push_back(q);
+      if (gemm_ws) ptrs.push_back(gemm_ws);
       out->arena_bytes = slab_total;
       out->arena_backend = ptrs.empty() ? 0 : GP_ARENA_MALLOC;
       out->free_deferred = !ptrs.empty();
@@ -523,15 +526,11 @@ static int probe_device_impl(Ctx* ctx, const char* uuid, uint32_t mask, gp_devic
       // a small buffer of its own (a millisecond to allocate).  The provider thread starts once the timed launches
       // are over: allocating DURING them was tried first and cost the GEMM 9 % of its median.
       const auto a0 = std::chrono::steady_clock::now();
-      void* ws = nullptr;
-      cudaError_t e = cudaMalloc(&ws, gemm_need);
+      cudaError_t e = cudaMalloc(&gemm_ws, gemm_need);
       d->alloc_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - a0).count();
-      if (e != cudaSuccess) return fail(cuda_fail(e, "cudaMalloc(gemm workspace)", &out->detail));
-      rc = run_gemm(reinterpret_cast<uint8_t*>(ws), &start_provider);
+      if (e != cudaSuccess) { gemm_ws = nullptr; return fail(cuda_fail(e, "cudaMalloc(gemm workspace)", &out->detail)); }
+      rc = run_gemm(reinterpret_cast<uint8_t*>(gemm_ws), &start_provider);
       start_provider();  // (if the GEMM failed before its timed launches ended)
-      cudaStreamSynchronize(d->stream);
-      cudaFree(ws);
-      (void)cudaGetLastError();
       if (rc) return fail(rc);
     } else {
       // (grow before the provider starts: both would otherwise wait for the same reaper thread)
