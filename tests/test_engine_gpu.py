@@ -201,3 +201,19 @@ def test_sticky_fault_marks_the_device_lost_and_reset_recovers(tmp_path):
     pkg = os.path.dirname(os.path.dirname(gpuprobe.__file__))
     r = subprocess.run([sys.executable, "-c", _POISON_SCRIPT, pkg], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "poison-reset ok" in r.stdout, (r.stdout, r.stderr)
+
+
+def test_cold_probe_that_runs_out_of_memory_cleans_up():
+    """Three 80 GiB slabs do not fit a 180 GB card: the third allocation fails on the provider thread while the
+    call is already working.  The call must come back with GP_ERR_NOMEM (not hang, not crash), and the two slabs
+    it did get must be back with the driver afterwards — the next, ordinary probe succeeds."""
+    import torch
+    with gpuprobe.Probe(hbm_bytes=80 << 30, iters=1, warmup=1, arena_cap_bytes=400 << 30) as p:
+        with pytest.raises(gpuprobe.GpuProbeError) as e:
+            p.probe_device("0", gpuprobe.GP_PROBE_TRIAD)
+        assert e.value.code == gpuprobe.GP_ERR_NOMEM
+        p.trim()  # joins the release thread
+        free, total = torch.cuda.mem_get_info(0)
+        assert free > total - (24 << 30)
+    with gpuprobe.Probe(hbm_bytes=1 << 30, iters=1, warmup=1, wo_passes=1) as p:
+        assert p.probe_device("0", gpuprobe.GP_PROBE_ALL_SINGLE).healthy == 1

@@ -115,8 +115,14 @@ def test_manager_leaves_a_gpu_with_a_tenant_alone():
     """The same start-up path WITHOUT --assume-idle: this pytest process holds a CUDA context on GPU 0, so NVML
     reports a tenant there.  loadPlugins must not give that GPU the full probe (it keeps Healthy, ungraded) and
     must not run the fabric probe, which would drive every GPU at once."""
+    import sys
     import torch
     torch.zeros(1, device="cuda:0")   # make sure the tenant exists
+    sys.path.insert(0, os.path.join(ROOT, "k8s-gpu-device-plugin_b200"))
+    import gpuprobe
+    with gpuprobe.Probe() as p:
+        if not p.nvml_snapshot(p.device_uuid(0)).available:
+            pytest.skip("NVML not loadable on this box: busy-ness cannot be told")
     d = run_sim("--scenario", "manager", "--fabric-mib", "64")
     assert d["devices"] >= 1 and d["unhealthy"] == 0 and d["busy_skipped"] >= 1
     assert d["fabric"]["ngpus"] == 0
