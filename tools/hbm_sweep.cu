@@ -392,7 +392,8 @@ int main(int argc, char** argv) {
   const int sm = p.multiProcessorCount;
   printf("# %s, %d SMs, N = %llu GiB per array\n", p.name, sm, (unsigned long long)(N >> 30));
   uint8_t *a, *b;
-  CK(cudaMalloc(&a, N)); CK(cudaMalloc(&b, N));
+  const uint64_t kPad = 256ull << 20;  // room for the offset experiments (r2 off*)
+  CK(cudaMalloc(&a, N)); CK(cudaMalloc(&b, N + kPad));
   CK(cudaMemset(a, 1, N)); CK(cudaMemset(b, 2, N));
   uint64_t* out; CK(cudaMalloc(&out, 8)); CK(cudaMemset(out, 0, 8));
   cudaStream_t s; CK(cudaStreamCreate(&s));
@@ -447,7 +448,12 @@ int main(int argc, char** argv) {
     for (uint64_t off = 0; off + W <= N; off += W) { /* W must divide N: a partial window is skipped, never overrun */ \
       if (off + 2 * W <= N) l2_pull_window<<<(unsigned)(W / 16384 / 64), 64, 0, st>>>(a + off + W, W); \
       copy_tma_np<16384, 4><<<(unsigned)(W / 65536), 32, 65536, st>>>(a + off, b + off); } }})
-  COPY_WINDOWED(32); COPY_WINDOWED(64);  // (96 MiB does not divide the array; 128 MiB no longer fits L2)
+  COPY_WINDOWED(32); COPY_WINDOWED(64);
+  // (c) does the distance between the arrays matter (a power-of-two distance could put src[i] and dst[i] in the same
+  // bank)?  Same kernel, destination shifted by an odd number of KiB / MiB inside a padded allocation.
+  printf("# a = %p  b = %p  (b - a = %lld MiB)\n", (void*)a, (void*)b, (long long)((b - a) >> 20));
+#define COPY_OFF(OFFKIB) cases.push_back({"r2 off copy_tma_np tile16384 nt4, dst + " #OFFKIB " KiB", 2.0 * N, [=](cudaStream_t st) { copy_tma_np<16384, 4><<<(unsigned)(N / 65536), 32, 65536, st>>>(a, b + (uint64_t)OFFKIB * 1024); }})
+  COPY_OFF(0); COPY_OFF(64); COPY_OFF(1088); COPY_OFF(4160); COPY_OFF(33856); COPY_OFF(133184); COPY_OFF(16); COPY_OFF(2048);  // (96 MiB does not divide the array; 128 MiB no longer fits L2)
   { const uint64_t NT3 = N / 2; float* fa = (float*)a; float* fb = (float*)b; float* fc = (float*)(b + NT3);
 #define TRIAD_NP(U, T) cases.push_back({"triad_np U" #U " t" #T, 3.0 * NT3, [=](cudaStream_t st) { triad_np<U><<<(unsigned)(NT3 / 32 / (T * U)), T, 0, st>>>(fa, fb, fc, 3.0f); }})
     TRIAD_NP(1, 256); TRIAD_NP(2, 256); TRIAD_NP(4, 256); TRIAD_NP(2, 512); TRIAD_NP(1, 512); TRIAD_NP(2, 128); TRIAD_NP(1, 1024);
