@@ -15,10 +15,11 @@
 //
 // Either way the driver serialises memory management across threads and processes (eight processes
 // freeing 48 GiB at once: 225 ms, SCALE_r01), so what cannot be avoided is taken off the caller's
-// path: a cold probe hands its arena to a reaper thread and returns (free_arena_deferred; the next
-// call on the device joins it first), and gp_probe_device grows the big arena on a helper thread
-// while the GEMM probe runs in a small buffer of its own.  Device::alloc_s / free_s report the host
-// time the call really spent blocked on the allocator.
+// path: a cold probe hands its memory to a reaper thread and returns (free_arena_deferred /
+// free_buffers_deferred; the next call on the device joins it first), and a cold gp_probe_device does
+// not use this arena at all: it takes three cudaMalloc slabs, allocated in order on a provider thread
+// behind the probes that do not need them yet (engine.cu, probe_device_impl).  Device::alloc_s /
+// free_s report the host time a call really spent blocked on the allocator.
 #include <cuda.h>
 
 #include <chrono>
