@@ -112,7 +112,10 @@ enum {
 /* test-only fault injection (gp_config.test_fault); nothing here touches the hardware abnormally */
 enum {
   GP_TEST_FAULT_GEMM_SKIP_TILE = 1u << 0, /* after the launches, one 256 x 256 tile of C is put back to its NaN fill */
-  GP_TEST_FAULT_GEMM_FLIP_BIT = 1u << 1   /* one low mantissa bit of one element of the timed C is flipped */
+  GP_TEST_FAULT_GEMM_FLIP_BIT = 1u << 1,  /* one low mantissa bit of one element of the timed C is flipped */
+  GP_TEST_FAULT_P2P_CORRUPT = 1u << 2     /* one bit of one word of the last GPU's P2P source buffer is flipped after the
+                                           * fill: whoever reads it must notice (gp_probe_p2p fails, the fabric verdict
+                                           * reports data_ok = 0) */
 };
 
 /* arena backends (gp_config.arena_backend) */

@@ -321,6 +321,8 @@ static int p2p_probe_locked(Ctx* ctx, int ngpus, size_t bytes, int dir, double* 
     d->triad_operands_bytes = 0;
     // what every reader must find: the address pattern, word index from the arena base
     CU_OR_RETURN(launch_pattern_fill(reinterpret_cast<uint64_t*>(d->arena), bytes / 8, GP_PAT_ADDRESS, 0, d->sm_count, d->stream));
+    if ((ctx->cfg.test_fault & GP_TEST_FAULT_P2P_CORRUPT) && i == ngpus - 1 && bytes >= 4096)  // test hook: one wrong bit
+      CU_OR_RETURN(launch_bitflip(reinterpret_cast<uint64_t*>(d->arena), bytes / 16 + 3, 17, d->stream));
     if (copy_engine) CU_OR_RETURN(cudaMemsetAsync(d->arena + bytes, 0x5A, bytes, d->stream));
     CU_OR_RETURN(cudaMemsetAsync(d->d_count, 0, sizeof(unsigned long long), d->stream));
     CU_OR_RETURN(cudaStreamSynchronize(d->stream));

@@ -35,7 +35,7 @@ GP_ERR_NOMEM, GP_ERR_UNSUPPORTED, GP_ERR_STRUCT_SIZE, GP_ERR_TOO_LARGE = -5, -6,
 GP_ERR_DEVICE_LOST = -9
 GP_ARENA_AUTO, GP_ARENA_VMM, GP_ARENA_MALLOC = 0, 1, 2
 GP_GEMM_AUTO, GP_GEMM_1CTA_128x256, GP_GEMM_2CTA_256x256, GP_GEMM_2CTA_256x512 = 0, 1, 2, 3
-GP_TEST_FAULT_GEMM_SKIP_TILE, GP_TEST_FAULT_GEMM_FLIP_BIT = 1, 2
+GP_TEST_FAULT_GEMM_SKIP_TILE, GP_TEST_FAULT_GEMM_FLIP_BIT, GP_TEST_FAULT_P2P_CORRUPT = 1, 2, 4
 GP_P2P_READ, GP_P2P_WRITE, GP_P2P_BIDIR_WRITE, GP_P2P_ALL_AT_ONCE = 0, 1, 2, 3
 GP_P2P_BIDIR_READ, GP_P2P_COPY_ENGINE, GP_P2P_COPY_ENGINE_BIDIR = 4, 5, 6
 GP_FABRIC_MAX_GPUS = 16

@@ -118,3 +118,22 @@ def test_fabric_verdict_pairs():
                         min_allreduce_busbw_gbps=1e6) as p:
         f = p.probe_fabric(n)
         assert f.healthy == 0 and (f.failed & 1) and (f.failed & 4) and f.data_ok == 1
+
+
+def test_a_read_that_returns_wrong_bytes_is_noticed():
+    """One flipped bit in 64 MiB of a source buffer (test hook): the read that loads it folds a different sum and
+    xor than the closed form of the pattern, so gp_probe_p2p fails instead of reporting a bandwidth, the copy-engine
+    mode finds the word where it landed, and the fabric verdict says data_ok = 0 / unhealthy — on however many GPUs
+    there are (with one, the reader is the GPU itself)."""
+    import torch  # noqa: F401
+    with gpuprobe.Probe(keep_arena=1, fabric_bytes=64 << 20, test_fault=gpuprobe.GP_TEST_FAULT_P2P_CORRUPT) as p:
+        n = p.device_count()
+        for mode in (gpuprobe.GP_P2P_READ, gpuprobe.GP_P2P_COPY_ENGINE):
+            with pytest.raises(gpuprobe.GpuProbeError) as e:
+                p.probe_p2p(n, 64 << 20, mode)
+            assert e.value.code == gpuprobe.GP_ERR_CUDA and ("wrong bytes" in e.value.detail or "did not land intact" in e.value.detail)
+        f = p.probe_fabric(n)
+        assert f.data_ok == 0 and f.healthy == 0 and (f.failed & 8)
+    with gpuprobe.Probe(keep_arena=1, fabric_bytes=64 << 20) as p:   # the same without the fault is clean
+        f = p.probe_fabric(p.device_count())
+        assert f.data_ok == 1 and f.healthy == 1
